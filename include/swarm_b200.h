@@ -1,0 +1,185 @@
+/*
+ * swarm_b200.h — C ABI of the B200-native batched drone-swarm coverage environment.
+ *
+ * This is the drop-in boundary for ONE hot path of grohith327/MARL-Drones: the headless 2D
+ * environment `DroneEnv.reset()/step()` (reference: A2C/noVis_sim.py:7-175 and
+ * DQL_model/noVis_sim.py:7-168) and the stacked, auto-resetting vec-env surface around it
+ * (reference: A2C/envs.py:17-41,58-117).  The reference has no FFI on this path — the
+ * boundary there is the Python class — so these entry points are what a `ctypes` binding
+ * on the reference side calls (see INTEGRATION.md for the stub).
+ *
+ * Conventions
+ *  - every function returns int: 0 = SWARM_OK, negative = SwarmStatus error; no C++
+ *    exception crosses the ABI; `swarm_strerror` turns a status into text.
+ *  - the library owns the opaque handle and the resident struct-of-arrays state; the
+ *    caller owns every input / output buffer.  Unless a name ends in `_host`, buffers are
+ *    DEVICE pointers on the handle's device and all work is enqueued asynchronously on
+ *    the `stream` argument (a `cudaStream_t` passed as `void*`; NULL = legacy default stream).
+ *    No hidden synchronisation: every device entry point is CUDA-graph capturable.
+ *  - invalid actions do not trap; they set a sticky device error word that
+ *    `swarm_device_error` reads (the Python facade turns it into the reference's
+ *    AssertionError, A2C/noVis_sim.py:118-120).
+ *  - a handle is not thread-safe; one handle per device; multi-GPU = one handle per rank
+ *    (`env_id_base` keys the RNG by GLOBAL env id, so any sharding yields identical envs).
+ *
+ * Layouts (N envs, D drones, R=row_count, C=col_count)
+ *  - boundary grid      int8  [N][C][R]   grid[n][y][x] = reference `grid[x][y]`
+ *                                         (== the reference obs order `np.array(grid).T.flatten()`,
+ *                                         A2C/noVis_sim.py:168-170), values {0, 1, uncertainity}
+ *  - positions          float [N][D][2]   (x, y) = reference `n_drones_pos[i]`
+ *  - meta               int32 [N][4]      {step_func_count, remaining(#cells>0), episode_return, episode}
+ *  - dwell counters     int16 [N][C][R]   only when dwell_normal|dwell_anom != 0
+ *  - obs FULL           T     [N][R*C]    obs[n][y*R+x]                (T = float32 or uint8)
+ *  - obs WINDOW         T     [N][D][W*W] win[n][i][b*W+a] = grid[cx-h+a][cy-h+b], pad -1 (255 for uint8)
+ *  - resident grid (private) is 2 bits / cell, 16 cells per uint32, flat index y*R+x.
+ */
+#ifndef SWARM_B200_H_
+#define SWARM_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SWARM_ABI_VERSION 1
+
+typedef enum SwarmStatus {
+  SWARM_OK = 0,
+  SWARM_ERR_INVALID_ARG = -1,   /* NULL pointer, bad range, bad enum            */
+  SWARM_ERR_CONFIG = -2,        /* unsupported SwarmConfig (see swarm_create)    */
+  SWARM_ERR_CUDA = -3,          /* a CUDA runtime call failed (swarm_last_cuda_error) */
+  SWARM_ERR_NO_DEVICE = -4,     /* no CUDA device / wrong architecture: there is NO CPU fallback */
+  SWARM_ERR_ALLOC = -5,
+  SWARM_ERR_NCCL = -6
+} SwarmStatus;
+
+enum { SWARM_REWARD_A2C = 0, SWARM_REWARD_DQL = 1 };   /* A2C/noVis_sim.py:141-152,172-173 vs DQL_model/noVis_sim.py:138-148 */
+enum { SWARM_OBS_FULL = 0, SWARM_OBS_WINDOW = 1 };     /* A2C/noVis_sim.py:168-170 vs SURVEY App. B.1 */
+enum { SWARM_DTYPE_F32 = 0, SWARM_DTYPE_U8 = 1 };      /* obs element type */
+enum { SWARM_ACT_U8 = 0, SWARM_ACT_I32 = 1, SWARM_ACT_I64 = 2 };
+
+/* device error word bits (sticky until swarm_device_error(clear=1)) */
+enum { SWARM_DEVERR_BAD_ACTION = 1 };
+
+/* statistics vector, int64[8], accumulated with atomics */
+enum {
+  SWARM_STAT_ENV_STEPS = 0, SWARM_STAT_AGENT_STEPS = 1, SWARM_STAT_REWARD_SUM = 2,
+  SWARM_STAT_EPISODES_DONE = 3, SWARM_STAT_EPISODE_LEN_SUM = 4, SWARM_STAT_EPISODE_RETURN_SUM = 5,
+  SWARM_STAT_CELLS_MAPPED = 6, SWARM_STAT_ANOMALOUS_MAPPED = 7, SWARM_STAT_COUNT = 8
+};
+
+/* Mirrors the kwargs of DroneEnv.__init__ (A2C/noVis_sim.py:8-17) plus the batch fields. */
+typedef struct SwarmConfig {
+  int32_t struct_size;     /* = sizeof(SwarmConfig); ABI guard                                   */
+  int32_t n_envs;          /* N  (envs resident on this device)                                  */
+  int32_t n_drones;        /* D  n_drones        (reference default 3)                           */
+  int32_t row_count;       /* R  row_count       (10)                                            */
+  int32_t col_count;       /* C  col_count       (10)                                            */
+  int32_t n_anamolous;     /*    n_anamolous     (5)  [sic, reference spelling]                  */
+  int32_t uncertainity;    /* U  uncertainity    (5)  must be in [2,127]                         */
+  int32_t reward_mode;     /* SWARM_REWARD_*                                                     */
+  int32_t obs_mode;        /* SWARM_OBS_*                                                        */
+  int32_t window;          /* W, odd, WINDOW mode only (5)                                       */
+  int32_t obs_dtype;       /* SWARM_DTYPE_*                                                      */
+  int32_t auto_reset;      /* 1: reset on done and return the reset obs (A2C/envs.py:22-26)      */
+  int32_t dwell_normal;    /* swarmsim-2d/run_env.py:46  (0 = noVis behaviour)                   */
+  int32_t dwell_anom;      /* swarmsim-2d/run_env.py:47                                          */
+  int32_t device;          /* CUDA device ordinal                                                */
+  int32_t reserved0;
+  double  collision_dist;  /* cd collision_dist  (0.5)                                           */
+  double  step_size;       /* ss step_size       (0.5; every trainer passes 1.0)                 */
+  uint64_t seed;           /* Philox key for device resets                                       */
+  int64_t env_id_base;     /* global id of local env 0 (sharding: rank g owns [g*N, (g+1)*N))    */
+} SwarmConfig;
+
+typedef struct SwarmEnv SwarmEnv;   /* opaque */
+
+/* -- lifetime ------------------------------------------------------------------------------ */
+int swarm_abi_version(void);
+const char* swarm_strerror(int status);
+const char* swarm_last_cuda_error(void);
+/* Number of CUDA devices with compute capability 10.x visible to this process (0 = none). */
+int swarm_device_count(void);
+
+/* Allocates the resident state for cfg->n_envs envs on cfg->device and initialises every env
+ * (episode 0) exactly like DroneEnv.__init__ -> init_env (A2C/noVis_sim.py:34,36-63), with
+ * Philox4x32-10 keyed by (seed, env_id_base+n, episode) in place of the reference's global
+ * MT19937.  Rejects (SWARM_ERR_CONFIG): uncertainity outside [2,127], n_anamolous > R*C
+ * (the reference loops forever, noVis_sim.py:47-55), even/oversized window, R*C > 2^24,
+ * D > 1024. */
+int swarm_create(const SwarmConfig* cfg, SwarmEnv** out);
+int swarm_destroy(SwarmEnv* env);
+int swarm_get_config(const SwarmEnv* env, SwarmConfig* out);
+
+/* Elements of one obs tensor ([N][R*C] or [N][D][W*W]) and its byte size. */
+int64_t swarm_obs_elems(const SwarmEnv* env);
+int64_t swarm_obs_bytes(const SwarmEnv* env);
+
+/* Device pointers into the resident state (views stay valid until swarm_destroy):
+ * which = 0: positions float[N][D][2]; 1: meta int32[N][4]; 2: packed grid uint32[N][env_words];
+ * 3: device error word int32[1]; 4: internal statistics int64[8]. */
+int swarm_state_ptr(SwarmEnv* env, int which, void** ptr_out, int64_t* bytes_out);
+
+/* -- reset (DroneEnv.reset, A2C/noVis_sim.py:65-70; VecEnv.reset, A2C/envs.py:95-98) -------- */
+/* mask: NULL = every env, else uint8[N] (non-zero = reset).  Each reset env advances to its
+ * next episode.  obs_out may be NULL; otherwise the obs of ALL N envs is written. */
+int swarm_reset(SwarmEnv* env, const uint8_t* mask, void* obs_out, void* stream);
+
+/* -- state injection / extraction (parity harness, checkpoint) ------------------------------ */
+/* Buffers describe envs [first, first+count).  grid int8[count][C][R]; pos float[count][D][2];
+ * t int32[count] (step_func_count); wait int16[count][C][R] or NULL.  set_state recomputes
+ * `remaining`, zeroes the episode return and keeps the episode counter. */
+int swarm_set_state(SwarmEnv* env, const int8_t* grid, const float* pos, const int32_t* t,
+                    const int16_t* wait, int32_t first, int32_t count, void* stream);
+int swarm_get_state(SwarmEnv* env, int8_t* grid, float* pos, int32_t* t, int16_t* wait,
+                    int32_t first, int32_t count, void* stream);
+
+/* -- the hot path (DroneEnv.step, A2C/noVis_sim.py:112-175) --------------------------------- */
+/* actions[N][D] of action_dtype; obs_out as described above (may be NULL to skip emission);
+ * reward_out float[N]; done_out uint8[N]; stats_accum int64[8] or NULL (atomically accumulated;
+ * the caller zeroes it).  One fused kernel launch: move+clip -> coverage scatter with
+ * intra-warp conflict resolution -> reward/done reduction -> (auto-reset) -> obs emission. */
+int swarm_step(SwarmEnv* env, const void* actions, int action_dtype, void* obs_out,
+               float* reward_out, uint8_t* done_out, int64_t* stats_accum, void* stream);
+
+/* T consecutive steps in ONE launch: actions uint8[T][N][D]; obs_out [T][...] (or NULL, or
+ * only the last step's obs when obs_last_only != 0); reward_out float[T][N]; done_out uint8[T][N]. */
+int swarm_rollout(SwarmEnv* env, int32_t T, const uint8_t* actions, void* obs_out,
+                  int32_t obs_last_only, float* reward_out, uint8_t* done_out,
+                  int64_t* stats_accum, void* stream);
+
+/* Host-buffer form of swarm_step (what a CPU-side caller of the reference's VecEnv.step sees):
+ * copies actions H2D, steps, copies obs/reward/done D2H through internal staging buffers and
+ * synchronises `stream` before returning.  Host buffers should be pinned for full PCIe rate.
+ * obs_host may be NULL (observation stays on the device for an on-device policy). */
+int swarm_step_host(SwarmEnv* env, const uint8_t* actions_host, void* obs_host,
+                    float* reward_host, uint8_t* done_host, int64_t* stats_host, void* stream);
+
+/* -- per-stage entry points (unit parity of the four stages named in the north star) --------- */
+/* K1 action decode + move + clip (A2C/noVis_sim.py:117-135): updates resident positions. */
+int swarm_stage_move(SwarmEnv* env, const void* actions, int action_dtype, void* stream);
+/* K2 coverage scatter (A2C/noVis_sim.py:75-90,104-110) for the CURRENT positions; writes the
+ * per-env coverage reward (10 / 30 per newly mapped cell) as int32[N]. */
+int swarm_stage_scatter(SwarmEnv* env, int32_t* cover_reward_out, void* stream);
+/* K3 reward tail + spread + done (A2C/noVis_sim.py:92-102,141-166,172-173): consumes the
+ * int32[N] coverage reward, advances step_func_count, never auto-resets. */
+int swarm_stage_reward(SwarmEnv* env, const int32_t* cover_reward, float* reward_out,
+                       uint8_t* done_out, void* stream);
+/* K4 observation emission for the current state. */
+int swarm_stage_obs(SwarmEnv* env, void* obs_out, void* stream);
+
+/* -- scripted action source (swarmsim-2d/drone.py:29-58 restated on the noVis lattice) ------- */
+/* Greedy nearest-unmapped-cell pursuit restricted to the 4 noVis actions; writes uint8[N][D]. */
+int swarm_greedy_actions(SwarmEnv* env, uint8_t* actions_out, void* stream);
+
+/* -- diagnostics ---------------------------------------------------------------------------- */
+/* Synchronises `stream`, reads the sticky device error word; clears it when clear != 0. */
+int swarm_device_error(SwarmEnv* env, int32_t* code_out, int clear, void* stream);
+/* Number of kernel launches issued through this handle since creation. */
+int64_t swarm_launch_count(const SwarmEnv* env);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* SWARM_B200_H_ */
