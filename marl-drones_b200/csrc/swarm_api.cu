@@ -1,0 +1,392 @@
+// swarm_api.cu — the C ABI declared in include/swarm_b200.h (host side: validation, allocation, launches).
+// There is NO CPU fallback: without an sm_100 device swarm_create returns SWARM_ERR_NO_DEVICE.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "../../include/swarm_b200.h"
+#include "swarm_kernels.cuh"
+
+using namespace swarm;
+
+struct SwarmEnv {
+  SwarmConfig cfg;
+  DevParams p;
+  int ts;                 // tile size (lanes per env)
+  int sm_count;
+  long long launches;
+  unsigned long long* stats_dev;   // int64[8] internal statistics
+  // staging for swarm_step_host
+  uint8_t* h_act_dev;
+  void* h_obs_dev;
+  float* h_rew_dev;
+  uint8_t* h_done_dev;
+  int* cover_dev;
+};
+
+static thread_local char g_cuda_err[256] = "";
+
+#define CUDA_TRY(expr)                                                                         \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess) {                                                                   \
+      snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return SWARM_ERR_CUDA;                                                                   \
+    }                                                                                          \
+  } while (0)
+
+extern "C" int swarm_abi_version(void) { return SWARM_ABI_VERSION; }
+
+extern "C" const char* swarm_strerror(int s) {
+  switch (s) {
+    case SWARM_OK: return "ok";
+    case SWARM_ERR_INVALID_ARG: return "invalid argument";
+    case SWARM_ERR_CONFIG: return "unsupported SwarmConfig";
+    case SWARM_ERR_CUDA: return "CUDA runtime error (see swarm_last_cuda_error)";
+    case SWARM_ERR_NO_DEVICE: return "no sm_100 CUDA device: this library has no CPU fallback";
+    case SWARM_ERR_ALLOC: return "allocation failed";
+    case SWARM_ERR_NCCL: return "NCCL error";
+    default: return "unknown status";
+  }
+}
+extern "C" const char* swarm_last_cuda_error(void) { return g_cuda_err; }
+
+extern "C" int swarm_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  int ok = 0;
+  for (int i = 0; i < n; ++i) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10) ++ok;
+  }
+  return ok;
+}
+
+static int pick_tile(int D) {
+  int ts = 1;
+  while (ts < D && ts < 32) ts <<= 1;
+  return ts < 4 ? 4 : ts;
+}
+
+static int use_device(const SwarmEnv* e) {
+  int cur = -1;
+  CUDA_TRY(cudaGetDevice(&cur));
+  if (cur != e->cfg.device) CUDA_TRY(cudaSetDevice(e->cfg.device));
+  return SWARM_OK;
+}
+
+static int grid_blocks(const SwarmEnv* e, long long warps_needed) {
+  long long b = (warps_needed + 7) / 8;
+  long long cap = (long long)e->sm_count * 8;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
+  if (!c || !out) return SWARM_ERR_INVALID_ARG;
+  *out = nullptr;
+  if (c->struct_size != (int32_t)sizeof(SwarmConfig)) return SWARM_ERR_INVALID_ARG;
+  const long long RC = (long long)c->row_count * c->col_count;
+  if (c->n_envs < 1 || c->n_drones < 1 || c->n_drones > 1024 || c->row_count < 1 || c->col_count < 1 || RC > (1ll << 24))
+    return SWARM_ERR_CONFIG;
+  if (c->uncertainity < 2 || c->uncertainity > 127) return SWARM_ERR_CONFIG;
+  if (c->n_anamolous < 0 || c->n_anamolous > RC) return SWARM_ERR_CONFIG;
+  if (c->reward_mode != SWARM_REWARD_A2C && c->reward_mode != SWARM_REWARD_DQL) return SWARM_ERR_CONFIG;
+  if (c->obs_mode != SWARM_OBS_FULL && c->obs_mode != SWARM_OBS_WINDOW) return SWARM_ERR_CONFIG;
+  if (c->obs_mode == SWARM_OBS_WINDOW && (c->window < 1 || c->window > 31 || (c->window & 1) == 0)) return SWARM_ERR_CONFIG;
+  if (c->obs_dtype != SWARM_DTYPE_F32 && c->obs_dtype != SWARM_DTYPE_U8) return SWARM_ERR_CONFIG;
+  if (!(c->collision_dist >= 0.0) || c->collision_dist > 64.0 || !(c->step_size > 0.0)) return SWARM_ERR_CONFIG;
+  if (c->dwell_normal < 0 || c->dwell_anom < 0 || c->dwell_normal > 32767 || c->dwell_anom > 32767) return SWARM_ERR_CONFIG;
+  if (RC / c->step_size > 2.0e9) return SWARM_ERR_CONFIG;
+
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return SWARM_ERR_NO_DEVICE; }
+  if (c->device < 0 || c->device >= ndev) return SWARM_ERR_INVALID_ARG;
+  int major = 0, sms = 0;
+  CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, c->device));
+  if (major != 10) return SWARM_ERR_NO_DEVICE;   // kernels are sm_100a only
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+  CUDA_TRY(cudaSetDevice(c->device));
+
+  SwarmEnv* e = new (std::nothrow) SwarmEnv();
+  if (!e) return SWARM_ERR_ALLOC;
+  memset(e, 0, sizeof(*e));
+  e->cfg = *c;
+  e->sm_count = sms;
+  e->ts = pick_tile(c->n_drones);
+  DevParams& p = e->p;
+  p.N = c->n_envs; p.D = c->n_drones; p.R = c->row_count; p.C = c->col_count; p.RC = (int)RC;
+  p.U = c->uncertainity; p.n_anom = c->n_anamolous;
+  p.reward_mode = c->reward_mode; p.obs_mode = c->obs_mode; p.W = c->obs_mode == SWARM_OBS_WINDOW ? c->window : 1;
+  p.obs_dtype = c->obs_dtype; p.auto_reset = c->auto_reset;
+  p.dwell_normal = c->dwell_normal; p.dwell_anom = c->dwell_anom;
+  p.has_wait = (c->dwell_normal | c->dwell_anom) != 0;
+  p.punish_thr = (int)std::floor((double)RC / c->step_size);
+  p.cd_fast = c->collision_dist <= 0.5;
+  p.scan_m = (int)std::ceil(c->collision_dist) + 1;
+  p.env_words = (int)(((RC + 15) / 16 + 3) / 4 * 4);
+  p.obs_per_env = c->obs_mode == SWARM_OBS_FULL ? (int)RC : c->n_drones * c->window * c->window;
+  p.ss = (float)c->step_size; p.xmax = (float)(c->row_count - 1); p.ymax = (float)(c->col_count - 1);
+  p.cd = c->collision_dist;
+  p.spread_thr = (double)(c->row_count / c->n_drones);
+  p.seed_lo = (uint32_t)c->seed; p.seed_hi = (uint32_t)(c->seed >> 32);
+  p.env_id_base = c->env_id_base;
+
+  const size_t N = (size_t)p.N;
+  cudaError_t err = cudaSuccess;
+  auto alloc = [&](void** ptr, size_t bytes) { if (err == cudaSuccess) err = cudaMalloc(ptr, bytes ? bytes : 16); };
+  alloc((void**)&p.grid, N * p.env_words * sizeof(uint32_t));
+  alloc((void**)&p.pos, N * p.D * sizeof(float2));
+  alloc((void**)&p.meta, N * sizeof(int4));
+  if (p.has_wait) alloc((void**)&p.wait, N * RC * sizeof(int16_t));
+  alloc((void**)&p.err, 16);
+  alloc((void**)&e->stats_dev, 8 * sizeof(unsigned long long));
+  alloc((void**)&e->cover_dev, N * sizeof(int));
+  if (err != cudaSuccess) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaMalloc: %s", cudaGetErrorString(err));
+    swarm_destroy(e);
+    return SWARM_ERR_ALLOC;
+  }
+  cudaMemsetAsync(p.err, 0, 16, 0);
+  cudaMemsetAsync(e->stats_dev, 0, 64, 0);
+  cudaMemsetAsync(p.meta, 0, N * sizeof(int4), 0);
+  reset_kernel<<<grid_blocks(e, p.N), 256, 0, 0>>>(p, nullptr, 0);
+  e->launches++;
+  err = cudaStreamSynchronize(0);
+  if (err == cudaSuccess) err = cudaGetLastError();
+  if (err != cudaSuccess) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "create/reset_kernel: %s", cudaGetErrorString(err));
+    swarm_destroy(e);
+    return SWARM_ERR_CUDA;
+  }
+  *out = e;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_destroy(SwarmEnv* e) {
+  if (!e) return SWARM_ERR_INVALID_ARG;
+  cudaFree(e->p.grid); cudaFree(e->p.pos); cudaFree(e->p.meta); cudaFree(e->p.wait); cudaFree(e->p.err);
+  cudaFree(e->stats_dev); cudaFree(e->cover_dev);
+  cudaFree(e->h_act_dev); cudaFree(e->h_obs_dev); cudaFree(e->h_rew_dev); cudaFree(e->h_done_dev);
+  delete e;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_get_config(const SwarmEnv* e, SwarmConfig* out) {
+  if (!e || !out) return SWARM_ERR_INVALID_ARG;
+  *out = e->cfg;
+  return SWARM_OK;
+}
+
+extern "C" int64_t swarm_obs_elems(const SwarmEnv* e) { return e ? (int64_t)e->p.N * e->p.obs_per_env : 0; }
+extern "C" int64_t swarm_obs_bytes(const SwarmEnv* e) {
+  return e ? swarm_obs_elems(e) * (e->p.obs_dtype == SWARM_DTYPE_F32 ? 4 : 1) : 0;
+}
+
+extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* bytes_out) {
+  if (!e || !ptr_out) return SWARM_ERR_INVALID_ARG;
+  const size_t N = (size_t)e->p.N;
+  void* ptr = nullptr;
+  int64_t b = 0;
+  switch (which) {
+    case 0: ptr = e->p.pos; b = (int64_t)(N * e->p.D * sizeof(float2)); break;
+    case 1: ptr = e->p.meta; b = (int64_t)(N * sizeof(int4)); break;
+    case 2: ptr = e->p.grid; b = (int64_t)(N * e->p.env_words * 4); break;
+    case 3: ptr = e->p.err; b = 4; break;
+    case 4: ptr = e->stats_dev; b = 64; break;
+    default: return SWARM_ERR_INVALID_ARG;
+  }
+  *ptr_out = ptr;
+  if (bytes_out) *bytes_out = b;
+  return SWARM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ launches
+template <typename OT>
+static void launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
+  const DevParams& p = e->p;
+  const int epw = 32 / e->ts;
+  const int blocks = grid_blocks(e, (p.N + epw - 1) / epw);
+  switch (e->ts) {
+    case 4: step_kernel<4, OT><<<blocks, 256, 0, st>>>(p, io); break;
+    case 8: step_kernel<8, OT><<<blocks, 256, 0, st>>>(p, io); break;
+    case 16: step_kernel<16, OT><<<blocks, 256, 0, st>>>(p, io); break;
+    default: step_kernel<32, OT><<<blocks, 256, 0, st>>>(p, io); break;
+  }
+  e->launches++;
+}
+
+static int launch_step(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
+  if (e->p.obs_dtype == SWARM_DTYPE_F32) launch_step_ot<float>(e, io, st);
+  else launch_step_ot<uint8_t>(e, io, st);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+static StepIO make_io(int flags) {
+  StepIO io;
+  memset(&io, 0, sizeof(io));
+  io.T = 1;
+  io.flags = flags;
+  return io;
+}
+
+extern "C" int swarm_reset(SwarmEnv* e, const uint8_t* mask, void* obs_out, void* stream) {
+  if (!e) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  reset_kernel<<<grid_blocks(e, e->p.N), 256, 0, st>>>(e->p, mask, 1);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (obs_out) {
+    StepIO io = make_io(F_OBS);
+    io.obs_out = obs_out;
+    return launch_step(e, io, st);
+  }
+  return SWARM_OK;
+}
+
+extern "C" int swarm_set_state(SwarmEnv* e, const int8_t* grid, const float* pos, const int32_t* t, const int16_t* wait,
+                               int32_t first, int32_t count, void* stream) {
+  if (!e || first < 0 || count < 0 || (long long)first + count > e->p.N) return SWARM_ERR_INVALID_ARG;
+  if (count == 0) return SWARM_OK;
+  int rc = use_device(e);
+  if (rc) return rc;
+  set_state_kernel<<<grid_blocks(e, count), 256, 0, (cudaStream_t)stream>>>(e->p, grid, pos, t, wait, first, count);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_get_state(SwarmEnv* e, int8_t* grid, float* pos, int32_t* t, int16_t* wait, int32_t first, int32_t count,
+                               void* stream) {
+  if (!e || first < 0 || count < 0 || (long long)first + count > e->p.N) return SWARM_ERR_INVALID_ARG;
+  if (count == 0) return SWARM_OK;
+  int rc = use_device(e);
+  if (rc) return rc;
+  get_state_kernel<<<grid_blocks(e, count), 256, 0, (cudaStream_t)stream>>>(e->p, grid, pos, t, wait, first, count);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_step(SwarmEnv* e, const void* actions, int action_dtype, void* obs_out, float* reward_out,
+                          uint8_t* done_out, int64_t* stats_accum, void* stream) {
+  if (!e || !actions || !reward_out || !done_out || action_dtype < 0 || action_dtype > 2) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
+  io.actions = actions; io.act_dtype = action_dtype; io.obs_out = obs_out;
+  io.reward_out = reward_out; io.done_out = done_out; io.stats = (unsigned long long*)stats_accum;
+  return launch_step(e, io, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_rollout(SwarmEnv* e, int32_t T, const uint8_t* actions, void* obs_out, int32_t obs_last_only,
+                             float* reward_out, uint8_t* done_out, int64_t* stats_accum, void* stream) {
+  if (!e || T < 1 || !actions || !reward_out || !done_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
+  io.T = T;
+  io.actions = actions; io.act_dtype = SWARM_ACT_U8; io.obs_out = obs_out; io.obs_last_only = obs_last_only ? 1 : 0;
+  io.reward_out = reward_out; io.done_out = done_out; io.stats = (unsigned long long*)stats_accum;
+  return launch_step(e, io, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_step_host(SwarmEnv* e, const uint8_t* actions_host, void* obs_host, float* reward_host, uint8_t* done_host,
+                               int64_t* stats_host, void* stream) {
+  if (!e || !actions_host || !reward_host || !done_host) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t N = (size_t)e->p.N, nact = N * e->p.D;
+  if (!e->h_act_dev) {
+    CUDA_TRY(cudaMalloc((void**)&e->h_act_dev, nact));
+    CUDA_TRY(cudaMalloc((void**)&e->h_rew_dev, N * sizeof(float)));
+    CUDA_TRY(cudaMalloc((void**)&e->h_done_dev, N));
+  }
+  if (obs_host && !e->h_obs_dev) CUDA_TRY(cudaMalloc(&e->h_obs_dev, (size_t)swarm_obs_bytes(e)));
+  CUDA_TRY(cudaMemcpyAsync(e->h_act_dev, actions_host, nact, cudaMemcpyHostToDevice, st));
+  if (stats_host) CUDA_TRY(cudaMemsetAsync(e->stats_dev, 0, 64, st));
+  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
+  io.actions = e->h_act_dev; io.act_dtype = SWARM_ACT_U8; io.obs_out = obs_host ? e->h_obs_dev : nullptr;
+  io.reward_out = e->h_rew_dev; io.done_out = e->h_done_dev; io.stats = stats_host ? e->stats_dev : nullptr;
+  rc = launch_step(e, io, st);
+  if (rc) return rc;
+  if (obs_host) CUDA_TRY(cudaMemcpyAsync(obs_host, e->h_obs_dev, (size_t)swarm_obs_bytes(e), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(reward_host, e->h_rew_dev, N * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(done_host, e->h_done_dev, N, cudaMemcpyDeviceToHost, st));
+  if (stats_host) CUDA_TRY(cudaMemcpyAsync(stats_host, e->stats_dev, 64, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return SWARM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ stages
+extern "C" int swarm_stage_move(SwarmEnv* e, const void* actions, int action_dtype, void* stream) {
+  if (!e || !actions || action_dtype < 0 || action_dtype > 2) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  const long long n = (long long)e->p.N * e->p.D;
+  long long b = (n + 255) / 256;
+  if (b > e->sm_count * 8) b = e->sm_count * 8;
+  move_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(e->p, actions, action_dtype);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_stage_scatter(SwarmEnv* e, int32_t* cover_reward_out, void* stream) {
+  if (!e || !cover_reward_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  StepIO io = make_io(F_SCATTER);
+  io.cover_out = cover_reward_out;
+  return launch_step(e, io, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_stage_reward(SwarmEnv* e, const int32_t* cover_reward, float* reward_out, uint8_t* done_out, void* stream) {
+  if (!e || !cover_reward || !reward_out || !done_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  StepIO io = make_io(F_REWARD);
+  io.cover_in = cover_reward; io.reward_out = reward_out; io.done_out = done_out;
+  return launch_step(e, io, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_stage_obs(SwarmEnv* e, void* obs_out, void* stream) {
+  if (!e || !obs_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  StepIO io = make_io(F_OBS);
+  io.obs_out = obs_out;
+  return launch_step(e, io, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_greedy_actions(SwarmEnv* e, uint8_t* actions_out, void* stream) {
+  if (!e || !actions_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  const long long n = (long long)e->p.N * e->p.D;
+  long long b = (n + 255) / 256;
+  if (b > e->sm_count * 8) b = e->sm_count * 8;
+  greedy_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(e->p, actions_out);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_device_error(SwarmEnv* e, int32_t* code_out, int clear, void* stream) {
+  if (!e || !code_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemcpyAsync(code_out, e->p.err, 4, cudaMemcpyDeviceToHost, st));
+  if (clear) CUDA_TRY(cudaMemsetAsync(e->p.err, 0, 4, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return SWARM_OK;
+}
+
+extern "C" int64_t swarm_launch_count(const SwarmEnv* e) { return e ? e->launches : 0; }

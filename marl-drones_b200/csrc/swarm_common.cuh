@@ -1,0 +1,78 @@
+// swarm_common.cuh — device-side parameter block and small helpers shared by every kernel.
+//
+// Resident layout in HBM (struct-of-arrays, one handle per GPU):
+//   grid  uint32 [N][env_words]   2 bits per cell, 16 cells per word, flat cell index c = y*R + x
+//                                 (the reference's obs order, A2C/noVis_sim.py:168-170);
+//                                 codes: 0 mapped (value 0), 1 normal (value 1), 2 anomalous (value U); cells
+//                                 past R*C in the last word are 0.  env_words is a multiple of 4 (16 B).
+//   pos   float2 [N][D]           (x, y) = reference n_drones_pos[i]
+//   meta  int4   [N]              {step_func_count, remaining (#cells > 0), episode_return, episode}
+//   wait  int16  [N][R*C]         dwell counters, only allocated when dwell_normal|dwell_anom != 0
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace swarm {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+enum : int { F_MOVE = 1, F_SCATTER = 2, F_REWARD = 4, F_OBS = 8, F_ALL = 15 };
+
+struct DevParams {
+  // configuration (mirrors DroneEnv.__init__, A2C/noVis_sim.py:8-17)
+  int N, D, R, C, RC, U, n_anom;
+  int reward_mode, obs_mode, W, obs_dtype, auto_reset;
+  int dwell_normal, dwell_anom, has_wait;
+  int punish_thr;     // floor(R*C / step_size): punish <=> step_func_count > punish_thr   (noVis_sim.py:141-143)
+  int cd_fast;        // collision_dist <= 0.5: at most one lattice cell can be hit
+  int scan_m;         // ceil(cd) + 1: half-width of the bounded scan window for cd > 0.5
+  int env_words;      // uint32 words per env in the packed grid
+  int obs_per_env;    // R*C or D*W*W
+  float ss, xmax, ymax;
+  double cd;          // collision_dist
+  double spread_thr;  // row_count // n_drones                                            (noVis_sim.py:100)
+  uint32_t seed_lo, seed_hi;
+  long long env_id_base;
+  // resident state
+  uint32_t* grid;
+  float2* pos;
+  int4* meta;
+  int16_t* wait;
+  int* err;
+};
+
+__device__ __forceinline__ uint32_t ld_grid(const uint32_t* p) { return __ldcg(p); }
+__device__ __forceinline__ void st_grid(uint32_t* p, uint32_t v) { __stcg(p, v); }
+
+__device__ __forceinline__ float code_to_f32(uint32_t code, float u) {
+  // 0 -> 0, 1 -> 1, 2 -> U, 3 -> pad (-1)
+  return (code & 2u) ? ((code & 1u) ? -1.0f : u) : (float)(code & 1u);
+}
+__device__ __forceinline__ uint32_t code_to_u8(uint32_t code, uint32_t u) {
+  return (code & 2u) ? ((code & 1u) ? 255u : u) : (code & 1u);
+}
+
+// ---- Philox4x32-10 (Salmon et al., SC'11); same constants/round structure as oracle_philox4x32_10 ----
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return c;
+}
+__device__ __forceinline__ uint4 draw_block(const DevParams& p, long long env_id, uint32_t episode, uint32_t block) {
+  return philox4x32_10(make_uint4((uint32_t)(unsigned long long)env_id, (uint32_t)((unsigned long long)env_id >> 32), episode, block),
+                       p.seed_lo, p.seed_hi);
+}
+
+// per-thread statistics accumulator; reduced once per CTA, 6 atomics per CTA
+struct StatAcc {
+  long long rew = 0, ret = 0, len = 0;
+  int done = 0, cells = 0, anom = 0;
+};
+
+}  // namespace swarm

@@ -1,0 +1,66 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/swarm_b200.h declares; no compute calls."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from swarm_b200 import _lib
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(REPO, "include", "swarm_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(swarm_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_header_symbols_exported():
+    L = _lib.lib()
+    syms = declared_symbols()
+    assert len(syms) >= 20
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/swarm_b200.h but not exported"
+    assert sorted(_lib.EXPORTED) == syms
+
+
+def test_config_struct_layout():
+    assert C.sizeof(_lib.SwarmConfig) == 96          # 16 int32 + 2 double + 2 x 64-bit
+    assert _lib.SwarmConfig.collision_dist.offset == 64 and _lib.SwarmConfig.env_id_base.offset == 88
+
+
+def test_strerror_and_version():
+    L = _lib.lib()
+    assert L.swarm_abi_version() == 1
+    assert L.swarm_strerror(0) == b"ok"
+    assert b"no CPU fallback" in L.swarm_strerror(-4)
+
+
+def test_invalid_args_rejected_without_gpu():
+    L = _lib.lib()
+    h = C.c_void_p()
+    assert L.swarm_create(None, C.byref(h)) == -1
+    cfg = _lib.SwarmConfig(struct_size=4)
+    assert L.swarm_create(C.byref(cfg), C.byref(h)) == -1
+    bad = _lib.SwarmConfig(C.sizeof(_lib.SwarmConfig), 4, 3, 10, 10, 5, 1, 0, 0, 5, 0, 1, 0, 0, 0, 0, 0.5, 0.5, 0, 0)
+    assert L.swarm_create(C.byref(bad), C.byref(h)) == -2          # uncertainity <= 1 is unsupported
+    bad.uncertainity, bad.n_anamolous = 5, 101
+    assert L.swarm_create(C.byref(bad), C.byref(h)) == -2          # the reference would loop forever (noVis_sim.py:47-55)
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device the product path must fail loudly (never route to the oracle)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    L = _lib.lib()
+    ok = _lib.SwarmConfig(C.sizeof(_lib.SwarmConfig), 4, 3, 10, 10, 5, 5, 0, 0, 5, 0, 1, 0, 0, 0, 0, 0.5, 0.5, 0, 0)
+    h = C.c_void_p()
+    assert L.swarm_create(C.byref(ok), C.byref(h)) == -4
+    from swarm_b200 import BatchedDroneEnv, SwarmError
+    with pytest.raises(SwarmError):
+        BatchedDroneEnv(4)
+    src = "".join(open(os.path.join(REPO, "marl-drones_b200", "swarm_b200", f)).read()
+                  for f in os.listdir(os.path.join(REPO, "marl-drones_b200", "swarm_b200")) if f.endswith(".py"))
+    assert "oracle" not in src.replace("never route to the oracle", ""), "product code must not reference the oracle"
