@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py — agent-steps/sec of the B200-native swarm env step (BASELINE.json metric), one JSON line on rank 0.
+
+    python bench.py --gpus 1 --steps 200 --warmup 10              # ours, N=1
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 200 --warmup 10                 # one rank per GPU, envs sharded, no data-path collective
+    python bench.py --impl reference --steps 3 --warmup 1         # the reference's CPU algorithm (oracle port) on host cores
+
+A "step" is one pass of the hot path (one fused swarm_step launch) over one batch of N envs.  Default workload is
+BASELINE.json configs[2] ("cfg3": 65536 envs x 16 drones, 64x64 grid, 5x5 local windows) — the configuration the
+1/2/4/8-GPU metric is quoted on; weak scaling (every rank owns --envs envs).  Inputs are resident in HBM for `value`;
+`e2e` goes through swarm_step_host with pinned HOST buffers (H2D actions, D2H obs/reward/done every step).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(REPO, "marl-drones_b200"))
+sys.path.insert(0, REPO)
+
+WORKLOADS = {
+    # name: (envs per GPU, kwargs)   — SURVEY §8d
+    "cfg2": (4096, dict(row_count=32, col_count=32, n_drones=4, step_size=1.0, obs_mode="full")),
+    "cfg3": (65536, dict(row_count=64, col_count=64, n_drones=16, step_size=1.0, obs_mode="window", window=5)),
+    "cfg4": (16384, dict(row_count=10, col_count=10, n_drones=8, step_size=1.0, obs_mode="full")),
+    "cfg5a": (1024, dict(row_count=256, col_count=256, n_drones=64, step_size=1.0, obs_mode="full")),
+    "cfg5b": (1024, dict(row_count=256, col_count=256, n_drones=64, step_size=1.0, obs_mode="window", window=5)),
+}
+METRIC = "agent-steps/sec (device-timed)"
+UNIT = "agent-steps/s"
+
+
+def algorithmic_bytes_per_env_step(kw, s_a=1, s_o=4):
+    """canonical, layout-independent bytes one env-step must move (1 B per grid cell)."""
+    D, RC = kw["n_drones"], kw["row_count"] * kw["col_count"]
+    if kw["obs_mode"] == "full":
+        return D * s_a + 16 * D + RC + D + RC * s_o + 21
+    WW = kw["window"] ** 2
+    return D * s_a + 16 * D + 2 * D + D * WW + D * WW * s_o + 21
+
+
+def load_peak():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def load_traffic(workload):
+    """DRAM bytes per launch of the step kernel from the committed ncu capture (profiles/traffic.json), else None."""
+    try:
+        return json.load(open(os.path.join(REPO, "profiles", "traffic.json"))).get(workload)
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_port_throughput(kw, budget_s=12.0, scan_mode=0, threads=0, steps=None):
+    """Times the oracle port of the reference algorithm (literal R*C scan per drone, A2C/noVis_sim.py:75-90) on the host
+    cores: a bounded sample of the same workload shape.  Returns (agent_steps_per_s, cores, sample description)."""
+    import numpy as np
+    from oracle.oracle import OracleBatch, lib
+    cores = threads or (lib().oracle_max_threads())
+    om = 0 if kw["obs_mode"] == "full" else 1
+    okw = dict(row_count=kw["row_count"], col_count=kw["col_count"], n_drones=kw["n_drones"], step_size=kw["step_size"],
+               obs_mode=om, window=kw.get("window", 5), auto_reset=True, seed=2026, scan_mode=scan_mode, nthreads=cores)
+    n_cpu = 8 * cores
+    o = OracleBatch(n_cpu, **okw)
+    rs = np.random.RandomState(1234)
+    acts = rs.randint(0, 4, (16, n_cpu, kw["n_drones"])).astype(np.uint8)
+    o.step(acts[0])
+    t0 = time.perf_counter(); o.step(acts[1]); dt = max(time.perf_counter() - t0, 1e-6)
+    T = steps if steps else max(2, min(20000, int(budget_s / dt)))
+    t0 = time.perf_counter()
+    for k in range(T):
+        o.step(acts[k % 16])
+    wall = time.perf_counter() - t0
+    v = n_cpu * kw["n_drones"] * T / wall
+    sample = (f"{n_cpu} envs x {T} steps of the workload shape, {'literal R*C scan' if scan_mode == 0 else 'bounded window'} "
+              f"C port of A2C/noVis_sim.py step (OpenMP, {cores} threads), {wall:.1f} s")
+    return v, cores, sample, wall / T
+
+
+def run_reference(args, kw, n_envs, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path (oracle port, all host threads), rank 0 only."""
+    if rank != 0:
+        return
+    steps, warm = max(args.steps, 1), max(args.warmup, 0)
+    import numpy as np
+    from oracle.oracle import OracleBatch, lib
+    cores = lib().oracle_max_threads()
+    om = 0 if kw["obs_mode"] == "full" else 1
+    n_cpu = 8 * cores
+    o = OracleBatch(n_cpu, row_count=kw["row_count"], col_count=kw["col_count"], n_drones=kw["n_drones"],
+                    step_size=kw["step_size"], obs_mode=om, window=kw.get("window", 5), auto_reset=True, seed=2026,
+                    scan_mode=0, nthreads=cores)
+    acts = np.random.RandomState(1234).randint(0, 4, (16, n_cpu, kw["n_drones"])).astype(np.uint8)
+    t0 = time.perf_counter(); o.step(acts[0]); dt = max(time.perf_counter() - t0, 1e-6)
+    inner = max(1, min(5000, int(120.0 / (steps + warm) / dt)))      # whole run stays within ~2 minutes
+    for w in range(warm):
+        for k in range(inner):
+            o.step(acts[k % 16])
+    t0 = time.perf_counter()
+    for s in range(steps):
+        for k in range(inner):
+            o.step(acts[k % 16])
+    wall = time.perf_counter() - t0
+    v = n_cpu * kw["n_drones"] * inner * steps / wall
+    sample = (f"each step = {inner} env-steps of {n_cpu} envs (bounded sample of {args.workload}), literal R*C-scan C port of "
+              f"A2C/noVis_sim.py (OpenMP, {cores} threads)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+        "ms_per_step": wall / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": args.workload, **{k: v2 for k, v2 in kw.items()}, "envs_per_step": n_cpu},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
+    ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
+    n_envs, kw = WORKLOADS[args.workload]
+    kw = dict(kw)
+    if args.envs:
+        n_envs = args.envs
+    if args.scaling == "strong":
+        n_envs = n_envs // world
+    if args.impl == "reference":
+        return run_reference(args, kw, n_envs, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from swarm_b200 import BatchedDroneEnv
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl ours) needs a B200; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    D = kw["n_drones"]
+    K, W = args.steps, max(args.warmup, 3)
+    envs = [BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=(rank * args.sets + s) * n_envs, **kw)
+            for s in range(args.sets)]
+    obs = [torch.empty(e.obs_shape, dtype=torch.float32, device=dev) for e in envs]
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    n_act = 8
+    acts = torch.randint(0, 4, (n_act, n_envs, D), dtype=torch.uint8, device=dev, generator=gen)
+    stream = torch.cuda.current_stream(dev)
+    side = torch.cuda.Stream(dev) if world > 1 else None
+    snap = torch.zeros(8, dtype=torch.int64, device=dev)
+
+    def one_step(i, ev=None):
+        s = i % args.sets
+        if ev is not None:
+            ev[0].record(stream)
+        envs[s].step(acts[i % n_act], out=obs[s])
+        if ev is not None:
+            ev[1].record(stream)
+        if world > 1:                       # the path's only collective: 64-byte episode statistics, off the critical path
+            snap.copy_(envs[s].stats, non_blocking=True)
+            done_ev = torch.cuda.Event(); done_ev.record(stream)
+            with torch.cuda.stream(side):
+                side.wait_event(done_ev)
+                dist.all_reduce(snap)
+
+    for i in range(W):
+        one_step(i)
+    torch.cuda.synchronize(dev)
+    launches0 = sum(e.launch_count for e in envs)
+    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_start.record(stream)
+    for i in range(K):
+        one_step(W + i, pairs[i])
+    if side is not None:
+        stream.wait_stream(side)
+    t_end.record(stream)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = t_start.elapsed_time(t_end)
+    launches = sum(e.launch_count for e in envs) - launches0
+    kern_ms = sorted(a.elapsed_time(b) for a, b in pairs)
+    kern_avg_ms = sum(kern_ms) / len(kern_ms)
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    total_agent_steps = float(n_envs) * D * K * world
+    value = total_agent_steps / (ms_total * 1e-3)
+
+    # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region)
+    e0 = envs[0]
+    a_h = torch.empty((n_act, n_envs, D), dtype=torch.uint8).pin_memory(); a_h.copy_(acts.cpu())
+    obs_h = torch.empty(e0.obs_shape, dtype=torch.float32).pin_memory()
+    rew_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
+    done_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
+    stats_h = torch.zeros(8, dtype=torch.int64).pin_memory()
+    E = max(1, args.e2e_steps)
+    for i in range(3):
+        envs[i % args.sets].step_host(a_h[i % n_act], obs_h, rew_h, done_h, stats_h)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    for i in range(E):
+        envs[i % args.sets].step_host(a_h[i % n_act], obs_h, rew_h, done_h, stats_h)
+    e2e_ms = (time.perf_counter() - w0) * 1e3
+    if world > 1:
+        t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    e2e_value = float(n_envs) * D * E * world / (e2e_ms * 1e-3)
+    h2d = n_envs * D
+    d2h = int(obs_h.numel() * 4 + n_envs * 4 + n_envs + 64)
+
+    if rank == 0:
+        peak, peak_src = load_peak()
+        bytes_per_launch = algorithmic_bytes_per_env_step(kw) * n_envs
+        achieved = bytes_per_launch / (kern_avg_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+            "dtype": "u2 grid codes / f32 positions+obs (integer rewards)", "data": "synthetic",
+            "config": {"workload": args.workload, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw,
+                       "obs_dtype": "float32", "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
+                       "actions": "uint8 uniform{0..3}, pre-generated on device",
+                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * 4 + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
+                       "parallelism": f"env-sharded x{world}, no data-path collective; 64 B stats all-reduce on a side stream"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": load_traffic(args.workload), "peak_source": peak_src, "kernel": "swarm::step_kernel",
+                         "kernel_ms_avg": kern_avg_ms, "kernel_ms_median": kern_ms[len(kern_ms) // 2],
+                         "algorithmic_bytes_per_launch": bytes_per_launch,
+                         "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw) / D},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": E, "ms_per_step": e2e_ms / E, "api": "swarm_step_host (pinned host buffers, full obs D2H)"},
+            "gpu_launches": launches, "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, sample, _ = cpu_port_throughput(kw, budget_s=12.0, scan_mode=0)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+            v2, _, sample2, _ = cpu_port_throughput(kw, budget_s=4.0, scan_mode=1)
+            line["cpu_baseline_windowed"] = {"value": v2, "unit": UNIT, "cores": cores, "kind": "port (ours: bounded-window scan, not the reference's algorithm)", "sample": sample2}
+        print(json.dumps(line))
+    for e in envs:
+        e.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

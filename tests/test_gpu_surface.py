@@ -1,0 +1,180 @@
+"""GPU: per-stage entry points, rollout, sharding invariance, host-buffer step and the single-env facade."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from common import SHAPES, env_kwargs, load_golden
+from oracle.oracle import OracleBatch
+from test_gpu_parity import assert_state_equal, make_pair
+
+pytestmark = pytest.mark.gpu
+
+
+def test_stage_entry_points_compose_to_step():
+    """K1 move -> K2 scatter -> K3 reward -> K4 obs == the fused step == the oracle."""
+    for kw in (dict(SHAPES["cfg2"]), dict(SHAPES["cfg3"]), dict(row_count=8, col_count=5, n_drones=9, collision_dist=1.2)):
+        N = 90
+        g, o = make_pair(N, seed=13, **kw)
+        rs = np.random.RandomState(1)
+        for k in range(150):
+            a = rs.randint(0, 4, (N, o.D)).astype(np.uint8)
+            g.stage_move(torch.from_numpy(a).cuda())
+            cover = g.stage_scatter()
+            rew, done = g.stage_reward(cover)
+            obs = g.stage_obs()
+            oo, orr, od = o.step(a)
+            assert np.array_equal(obs.reshape(N, -1).cpu().numpy(), oo), k
+            assert np.array_equal(rew.cpu().numpy(), orr) and np.array_equal(done.cpu().numpy(), od), k
+        assert_state_equal(g, o)
+        g.close()
+
+
+def test_stage_move_clips_like_np_clip():
+    g, o = make_pair(64, seed=2, row_count=4, col_count=6, n_drones=5, step_size=0.5)
+    for k in range(40):
+        a = np.full((64, 5), k % 4, np.uint8)
+        g.stage_move(torch.from_numpy(a).cuda())
+    p = g.pos.cpu().numpy()
+    assert p[..., 0].min() >= 0 and p[..., 0].max() <= 3 and p[..., 1].min() >= 0 and p[..., 1].max() <= 5
+    g.close()
+
+
+@pytest.mark.parametrize("cfg", ["cfg2", "cfg3", "cfg4"])
+def test_rollout_equals_steps(cfg):
+    kw = dict(SHAPES[cfg])
+    N, T = 77, 96
+    g1, o = make_pair(N, auto_reset=True, seed=17, **kw)
+    g2, _ = make_pair(N, auto_reset=True, seed=17, **kw)
+    a = torch.randint(0, 4, (T, N, o.D), dtype=torch.uint8, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+    obs_all = torch.empty((T,) + g1.obs_shape, dtype=torch.float32, device="cuda")
+    _, rew, done = g1.rollout(a, obs_out=obs_all)
+    for t in range(T):
+        ob, r, d, _ = g2.step(a[t])
+        assert torch.equal(ob, obs_all[t]), t
+        assert torch.equal(r, rew[t]) and torch.equal(d, done[t]), t
+        oo, orr, od = o.step(a[t].cpu().numpy())
+        assert np.array_equal(oo, obs_all[t].reshape(N, -1).cpu().numpy()), t
+    assert_state_equal(g1, o)
+    assert torch.equal(g1.stats, g2.stats)
+    last = torch.empty(g1.obs_shape, dtype=torch.float32, device="cuda")
+    g1.rollout(a, obs_out=last, obs_last_only=True)
+    for t in range(T):
+        ob, _, _, _ = g2.step(a[t])
+    assert torch.equal(last, ob)
+    g1.close(); g2.close()
+
+
+def test_sharding_invariance():
+    """Rank g of G owns envs [g*N/G, (g+1)*N/G): identical per-env trajectories for any G (RNG keyed by global env id)."""
+    kw = dict(SHAPES["cfg4"])
+    N, T = 96, 300
+    a = torch.randint(0, 4, (T, N, 8), dtype=torch.uint8, device="cuda", generator=torch.Generator("cuda").manual_seed(3))
+    whole, _ = make_pair(N, auto_reset=True, seed=23, **kw)
+    _, rew, done = whole.rollout(a)
+    for G in (2, 4, 8):
+        n = N // G
+        stats = torch.zeros(8, dtype=torch.int64, device="cuda")
+        for r in range(G):
+            shard, _ = make_pair(n, auto_reset=True, seed=23, env_id_base=r * n, **kw)
+            _, rr, dd = shard.rollout(a[:, r * n:(r + 1) * n].contiguous())
+            assert torch.equal(rr, rew[:, r * n:(r + 1) * n]) and torch.equal(dd, done[:, r * n:(r + 1) * n])
+            gg, gp, gt, _ = shard.get_state()
+            wg, wp, wt, _ = whole.get_state(r * n, n)
+            assert torch.equal(gg, wg) and torch.equal(gp, wp) and torch.equal(gt, wt)
+            stats += shard.stats
+            shard.close()
+        assert torch.equal(stats, whole.stats), G      # what the NCCL all-reduce of the 64-byte vector produces
+    whole.close()
+
+
+def test_step_host_matches_device_step():
+    kw = dict(SHAPES["cfg3"])
+    N = 200
+    g1, o = make_pair(N, auto_reset=True, seed=4, **kw)
+    a_h = torch.empty((N, 16), dtype=torch.uint8).pin_memory()
+    obs_h = torch.empty(g1.obs_shape, dtype=torch.float32).pin_memory()
+    rew_h = torch.empty(N, dtype=torch.float32).pin_memory()
+    done_h = torch.empty(N, dtype=torch.uint8).pin_memory()
+    stats_h = torch.zeros(8, dtype=torch.int64).pin_memory()
+    rs = np.random.RandomState(0)
+    for k in range(50):
+        a = rs.randint(0, 4, (N, 16)).astype(np.uint8)
+        a_h.copy_(torch.from_numpy(a))
+        g1.step_host(a_h, obs_h, rew_h, done_h, stats_h)
+        oo, orr, od = o.step(a)
+        assert np.array_equal(obs_h.numpy().reshape(N, -1), oo) and np.array_equal(rew_h.numpy(), orr)
+        assert np.array_equal(done_h.numpy(), od)
+    assert stats_h[0].item() == N and stats_h[1].item() == N * 16
+    g1.close()
+
+
+def test_greedy_actions_match_oracle_and_finish_episodes():
+    g, o = make_pair(33, auto_reset=False, seed=6, row_count=9, col_count=7, n_drones=3, step_size=1.0)
+    for k in range(80):
+        a = g.greedy_actions()
+        assert np.array_equal(a.cpu().numpy(), o.greedy_actions()), k
+        g.step(a)
+        o.step(a.cpu().numpy())
+    assert_state_equal(g, o)
+    assert int((g.meta[:, 1] == 0).sum()) == 33          # greedy pursuit maps a 9x7 grid with 3 drones in < 80 steps
+    g.close()
+
+
+# ------------------------------------------------------------------------------------------------ facade
+@pytest.mark.parametrize("name", ["cfg1_defaults_a2c", "cfg1_defaults_dql", "trainer_5x5_a2c", "cfg4_10x10_d8"])
+def test_facade_reproduces_reference_with_numpy_seed(name):
+    """np.random.seed(s); DroneEnv(**kw) -> the facade draws the reference's MT19937 stream in the reference's order, so
+    construction, reset-after-done and every step equal the golden trace of the live reference (3-tuple API)."""
+    from swarm_b200 import DQLDroneEnv, DroneEnv
+    gd = load_golden(name)
+    cfg = gd["config"]
+    kw, rm = env_kwargs(cfg)
+    np.random.seed(cfg["seed"])
+    env = (DroneEnv if rm == 0 else DQLDroneEnv)(**kw)
+    assert np.array_equal(np.array(env.grid, np.int8).T, gd["grid0"])
+    assert np.array_equal(np.array(env.n_drones_pos, np.float64), gd["pos0"])
+    assert env.action_size == 4 and env.state_size == kw["row_count"] * kw["col_count"]
+    T = gd["actions"].shape[0]
+    for k in range(T):
+        acts = [np.array([a]) for a in gd["actions"][k]] if k % 2 else [int(a) for a in gd["actions"][k]]   # A2C/train.py:73 vs :260
+        obs, r, d = env.step(acts)
+        assert obs.dtype == np.int64 and obs.shape == (env.state_size,)
+        assert np.array_equal(obs.astype(np.int8), gd["obs"][k]), k
+        assert isinstance(r, float) and r == gd["reward"][k] and isinstance(d, bool) and d == bool(gd["done"][k]), k
+        assert np.array_equal(np.array(env.n_drones_pos, np.float64), gd["pos"][k])
+        assert env.step_func_count == gd["t"][k]
+        if d and cfg["reset_on_done"]:
+            ob = env.reset()
+            i = list(gd["reset_steps"]).index(k)
+            assert np.array_equal(ob.astype(np.int8).reshape(kw["col_count"], kw["row_count"]), gd["reset_grid"][i])
+            assert np.array_equal(np.array(env.n_drones_pos, np.float64), gd["reset_pos"][i])
+    flags = env.uncertain_points
+    assert all(flags[k] == (1 if env.grid[k[0]][k[1]] != 0 else 0) for k in flags)
+    env.close()
+
+
+def test_facade_asserts_like_reference():
+    from swarm_b200 import DroneEnv
+    env = DroneEnv()
+    with pytest.raises(AssertionError, match="provide actions for each drone"):
+        env.step([0, 1])
+    with pytest.raises(AssertionError, match="action should be in range"):
+        env.step([0, 1, 4])
+    env.close()
+
+
+def test_launcher_installs_facade_module():
+    import sys
+    from swarm_b200 import launcher
+    saved = sys.modules.pop("noVis_sim", None)
+    try:
+        for variant, mode in (("A2C", "A2C"), ("DQL", "DQL")):
+            mod = launcher.install(variant)
+            from noVis_sim import DroneEnv
+            assert DroneEnv is mod.DroneEnv and DroneEnv.reward_mode == mode
+            del sys.modules["noVis_sim"]
+    finally:
+        if saved is not None:
+            sys.modules["noVis_sim"] = saved
