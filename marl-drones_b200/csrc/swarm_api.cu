@@ -13,7 +13,10 @@ using namespace swarm;
 struct SwarmEnv {
   SwarmConfig cfg;
   DevParams p;
-  int ts;                 // tile size (lanes per env)
+  int ts;                 // tile size (lanes per env) of the staged warp kernel
+  int staged;             // 1: swarm_warp.cuh kernel (grid staged in shared memory), 0: swarm_cta.cuh (one CTA per env)
+  int wpb;                // warps per block of the staged kernel
+  int smem_ok;            // dynamic shared-memory limit raised for this handle's kernel instantiation
   int sm_count;
   long long launches;
   unsigned long long* stats_dev;   // int64[8] internal statistics
@@ -63,10 +66,39 @@ extern "C" int swarm_device_count(void) {
   return ok;
 }
 
-static int pick_tile(int D) {
-  int ts = 1;
-  while (ts < D && ts < 32) ts <<= 1;
-  return ts < 4 ? 4 : ts;
+// ---- kernel selection ------------------------------------------------------------------------------------------------
+constexpr int kWarpSmemMax = 12 * 1024;     // per-warp shared-memory slice the staged kernel may use
+constexpr int kCtaSmemMax = 200 * 1024;
+
+static int stage_bytes_for(const SwarmConfig* c, int epw) {
+  if (c->obs_mode != SWARM_OBS_WINDOW) return 16;
+  const long long b = (long long)epw * c->n_drones * c->window * c->window * (c->obs_dtype == SWARM_DTYPE_F32 ? 4 : 1);
+  return (int)((b + 15) / 16 * 16);
+}
+
+// Smallest power-of-two tile >= D (min 4), widened while the batch would give too few warps to fill the GPU.
+// Returns 0 when the shape does not fit the staged kernel (D > 32 or the per-warp slice is too large).
+static int pick_tile(const SwarmConfig* c, int env_words, int sms, int* warp_smem_out, int* stage_out) {
+  if (c->n_drones > 32) return 0;
+  int ts = 4;
+  while (ts < c->n_drones) ts <<= 1;
+  while (ts < 32 && (long long)c->n_envs / (32 / ts) < (long long)sms * 16) ts <<= 1;
+  for (; ts <= 32; ts <<= 1) {
+    const int epw = 32 / ts;
+    const int stage = stage_bytes_for(c, epw);
+    const long long ws = (long long)stage + (long long)epw * env_words * 4 + 16;
+    if (ws <= kWarpSmemMax) {
+      *warp_smem_out = (int)ws;
+      *stage_out = stage;
+      return ts;
+    }
+  }
+  return 0;
+}
+
+template <typename K>
+static cudaError_t allow_smem(K kernel, int bytes) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 static int use_device(const SwarmEnv* e) {
@@ -115,7 +147,6 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   memset(e, 0, sizeof(*e));
   e->cfg = *c;
   e->sm_count = sms;
-  e->ts = pick_tile(c->n_drones);
   DevParams& p = e->p;
   p.N = c->n_envs; p.D = c->n_drones; p.R = c->row_count; p.C = c->col_count; p.RC = (int)RC;
   p.U = c->uncertainity; p.n_anom = c->n_anamolous;
@@ -131,6 +162,22 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   p.ss = (float)c->step_size; p.xmax = (float)(c->row_count - 1); p.ymax = (float)(c->col_count - 1);
   p.cd = c->collision_dist;
   p.spread_thr = (double)(c->row_count / c->n_drones);
+  {   // exact squared-distance thresholds: sqrt() is monotone, so  sqrt(z) < cd  <=>  z < cd2_thr  for every double z
+    double z = c->collision_dist * c->collision_dist;
+    while (z > 0.0 && std::sqrt(z) >= c->collision_dist) z = std::nextafter(z, -INFINITY);
+    while (std::sqrt(z) < c->collision_dist) z = std::nextafter(z, INFINITY);
+    p.cd2_thr = z;                                   // smallest z with sqrt(z) >= cd
+    z = p.spread_thr * p.spread_thr;
+    while (std::sqrt(z) <= p.spread_thr) z = std::nextafter(z, INFINITY);
+    while (z > 0.0 && std::sqrt(z) > p.spread_thr) z = std::nextafter(z, -INFINITY);
+    p.spread2_thr = z;                               // largest z with sqrt(z) <= row_count // n_drones
+  }
+  e->ts = pick_tile(c, p.env_words, sms, &p.warp_smem, &p.stage_bytes);
+  e->staged = e->ts != 0;
+  if (!e->staged) e->ts = 32;
+  e->wpb = 8;
+  while (e->wpb > 1 && (long long)e->wpb * p.warp_smem > kCtaSmemMax / 2) e->wpb >>= 1;   // keep >= 2 CTAs per SM
+  p.nq_magic = RC >= 4 ? (uint32_t)(((1ull << 32) + (uint64_t)(RC / 4) - 1) / (uint64_t)(RC / 4)) : 0u;
   p.seed_lo = (uint32_t)c->seed; p.seed_hi = (uint32_t)(c->seed >> 32);
   p.env_id_base = c->env_id_base;
 
@@ -204,23 +251,54 @@ extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* 
 }
 
 // ------------------------------------------------------------------------------------------------ launches
-template <typename OT>
-static void launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
+template <int TS, typename OT>
+static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st, int blocks, int smem) {
   const DevParams& p = e->p;
-  const int epw = 32 / e->ts;
-  const int blocks = grid_blocks(e, (p.N + epw - 1) / epw);
-  switch (e->ts) {
-    case 4: step_kernel<4, OT><<<blocks, 256, 0, st>>>(p, io); break;
-    case 8: step_kernel<8, OT><<<blocks, 256, 0, st>>>(p, io); break;
-    case 16: step_kernel<16, OT><<<blocks, 256, 0, st>>>(p, io); break;
-    default: step_kernel<32, OT><<<blocks, 256, 0, st>>>(p, io); break;
+  cudaError_t err;
+  if (p.obs_mode == SWARM_OBS_FULL) {
+    if (!e->smem_ok && (err = allow_smem(step_warp_kernel<TS, OT, 0, 0>, smem)) != cudaSuccess) return err;
+    step_warp_kernel<TS, OT, 0, 0><<<blocks, e->wpb * 32, smem, st>>>(p, io);
+  } else if (p.W == 5) {
+    if (!e->smem_ok && (err = allow_smem(step_warp_kernel<TS, OT, 1, 5>, smem)) != cudaSuccess) return err;
+    step_warp_kernel<TS, OT, 1, 5><<<blocks, e->wpb * 32, smem, st>>>(p, io);
+  } else {
+    if (!e->smem_ok && (err = allow_smem(step_warp_kernel<TS, OT, 1, 0>, smem)) != cudaSuccess) return err;
+    step_warp_kernel<TS, OT, 1, 0><<<blocks, e->wpb * 32, smem, st>>>(p, io);
+  }
+  return cudaSuccess;
+}
+
+template <typename OT>
+static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
+  const DevParams& p = e->p;
+  cudaError_t err = cudaSuccess;
+  if (e->staged) {
+    const int epw = 32 / e->ts;
+    const long long ngroups = ((long long)p.N + epw - 1) / epw;
+    long long blocks = (ngroups + e->wpb - 1) / e->wpb;
+    const long long cap = (long long)e->sm_count * 64;     // more CTAs than fit: the hardware scheduler balances the tail
+    if (blocks > cap) blocks = cap;
+    const int smem = e->wpb * p.warp_smem;
+    switch (e->ts) {
+      case 4: err = launch_warp_ts<4, OT>(e, io, st, (int)blocks, smem); break;
+      case 8: err = launch_warp_ts<8, OT>(e, io, st, (int)blocks, smem); break;
+      case 16: err = launch_warp_ts<16, OT>(e, io, st, (int)blocks, smem); break;
+      default: err = launch_warp_ts<32, OT>(e, io, st, (int)blocks, smem); break;
+    }
+  } else {
+    long long blocks = p.N;
+    const long long cap = (long long)e->sm_count * 8;       // 8 resident CTAs of 256 threads per SM, grid-stride beyond
+    if (blocks > cap) blocks = cap;
+    step_cta_kernel<OT><<<(int)blocks, 256, 0, st>>>(p, io);
   }
   e->launches++;
+  if (err == cudaSuccess) e->smem_ok = 1;
+  return err;
 }
 
 static int launch_step(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
-  if (e->p.obs_dtype == SWARM_DTYPE_F32) launch_step_ot<float>(e, io, st);
-  else launch_step_ot<uint8_t>(e, io, st);
+  if (e->p.obs_dtype == SWARM_DTYPE_F32) CUDA_TRY(launch_step_ot<float>(e, io, st));
+  else CUDA_TRY(launch_step_ot<uint8_t>(e, io, st));
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;
 }

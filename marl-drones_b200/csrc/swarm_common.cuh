@@ -31,6 +31,12 @@ struct DevParams {
   float ss, xmax, ymax;
   double cd;          // collision_dist
   double spread_thr;  // row_count // n_drones                                            (noVis_sim.py:100)
+  double cd2_thr;     // smallest double z with sqrt(z) >= cd:   sqrt(d2) < cd  <=>  d2 < cd2_thr   (exact, host-computed)
+  double spread2_thr; // largest double z with sqrt(z) <= spread_thr: sqrt(d2) > thr <=> d2 > spread2_thr
+  // warp-autonomous staged kernel (swarm_warp.cuh): per-warp shared-memory carve-up, bytes
+  int stage_bytes;    // obs staging (WINDOW mode), multiple of 16, >= 16
+  int warp_smem;      // stage_bytes + EPW*env_words*4 + 16
+  uint32_t nq_magic;  // ceil(2^32 / (RC/4)) for the FULL-mode vector -> (env, quad) split
   uint32_t seed_lo, seed_hi;
   long long env_id_base;
   // resident state
@@ -43,6 +49,42 @@ struct DevParams {
 
 __device__ __forceinline__ uint32_t ld_grid(const uint32_t* p) { return __ldcg(p); }
 __device__ __forceinline__ void st_grid(uint32_t* p, uint32_t v) { __stcg(p, v); }
+
+// ---- sm_90+/sm_100a async-copy (TMA bulk) and mbarrier wrappers -----------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+// orders this thread's earlier generic-proxy shared-memory accesses before later async-proxy (TMA) ones
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "SWARM_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra SWARM_DONE_%=;\n"
+      "bra SWARM_WAIT_%=;\n"
+      "SWARM_DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (bytes % 16 == 0, both addresses 16 B aligned), completion on `bar`   [SASS: UBLKCP]
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// shared -> global bulk store (same alignment rules), tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
 __device__ __forceinline__ float code_to_f32(uint32_t code, float u) {
   // 0 -> 0, 1 -> 1, 2 -> U, 3 -> pad (-1)

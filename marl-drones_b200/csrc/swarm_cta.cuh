@@ -1,0 +1,163 @@
+// swarm_cta.cuh — the fused env step for shapes the shared-memory-staged kernel does not take: more than 32 drones per
+// env, or a packed grid too large to stage per warp (the 256x256 stress config).  One CTA per env:
+//   warp 0 runs stages (1)-(3) on the HBM-resident grid in index-ordered chunks of 32 drones,
+//   then the WHOLE CTA streams stage (4) (a 256x256 full obs is 256 KiB per env: the emission is the kernel).
+// Reference lines per stage: see swarm_step.cuh.
+#pragma once
+#include "swarm_common.cuh"
+#include "swarm_emit.cuh"
+#include "swarm_step.cuh"
+
+namespace swarm {
+
+// Stages (1)-(3) (+ auto-reset) of one env by one warp.
+__device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc) {
+  constexpr int TS = 32;
+  const int flags = io.flags;
+  const int D = p.D;
+  const int nch = (D + TS - 1) / TS;
+  uint32_t* g = p.grid + (size_t)env * p.env_words;
+  int rew = 0, ncl = 0, nan = 0;
+  float x = 0.f, y = 0.f;   // chunk-0 drone of this lane (all drones when D <= 32)
+
+  for (int c = 0; c < nch; ++c) {
+    const int d = c * TS + lane;
+    const bool active = d < D;
+    float2 q = make_float2(0.f, 0.f);
+    if (active) {
+      float2* pp = p.pos + (size_t)env * D + d;
+      q = __ldcg(pp);
+      if (flags & F_MOVE) {   // stage (1), noVis_sim.py:117-135
+        const int a = load_action(io.actions, io.act_dtype, ((long long)t * p.N + env) * D + d);
+        if (a == 0) q.y -= p.ss;
+        else if (a == 1) q.x += p.ss;
+        else if (a == 2) q.y += p.ss;
+        else if (a == 3) q.x -= p.ss;
+        else atomicOr(p.err, 1);
+        q.x = fminf(fmaxf(q.x, 0.f), p.xmax);
+        q.y = fminf(fmaxf(q.y, 0.f), p.ymax);
+        __stcg(pp, q);
+      }
+    }
+    if (c == 0) { x = q.x; y = q.y; }
+    if ((flags & F_SCATTER) && p.cd_fast) {   // stage (2), cd <= 0.5: the only candidate is the nearest lattice cell
+      bool cand = false;
+      int cell = 0;
+      if (active) {
+        const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
+        const double dx = (double)cx - (double)q.x, dy = (double)cy - (double)q.y;
+        cand = dx * dx + dy * dy < p.cd2_thr;
+        cell = cy * p.R + cx;
+      }
+      const unsigned key = cand ? (unsigned)cell : (0x80000000u | (unsigned)lane);
+      const unsigned m = __match_any_sync(FULL, key);
+      if (cand && lane == __ffs(m) - 1) {
+        const int k = __popc(m);
+        uint32_t* wp = g + (cell >> 4);
+        const int sh = (cell & 15) * 2;
+        const uint32_t code = (ld_grid(wp) >> sh) & 3u;
+        if (code) {
+          bool clear = true;
+          if (p.has_wait) {   // dwell (App. B.2)
+            int16_t* w = p.wait + (size_t)env * p.RC + cell;
+            const int wv = *w;
+            if (wv >= k) { *w = (int16_t)(wv - k); clear = false; }
+            else if (wv > 0) *w = 0;
+          }
+          if (clear) {
+            atomicAnd(wp, ~(3u << sh));
+            rew += 10 + (code == 2u ? 20 : 0);   // 10 + _check_uncertain_mapped (noVis_sim.py:83-84,104-110)
+            ncl += 1;
+            nan += (code == 2u);
+          }
+        }
+      }
+      if (nch > 1) __syncwarp();   // later chunks see this chunk's clears (index order)
+    }
+  }
+  if ((flags & F_SCATTER) && !p.cd_fast) {
+    __syncwarp();
+    if (lane == 0) scatter_sequential(p, env, g, nullptr, rew, ncl, nan);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    rew += __shfl_xor_sync(FULL, rew, o);
+    ncl += __shfl_xor_sync(FULL, ncl, o);
+    nan += __shfl_xor_sync(FULL, nan, o);
+  }
+
+  if (flags & F_REWARD) {   // stage (3)
+    int4 m = make_int4(0, 0, 0, 0);
+    if (lane == 0) m = __ldcg(p.meta + env);
+    const int tcount = __shfl_sync(FULL, m.x, 0);
+    const bool punish = tcount > p.punish_thr;                    // noVis_sim.py:141-143 (count before increment)
+    const bool need = !punish;
+    bool spread = false;
+    __syncwarp();   // every chunk's position stores precede the D > 32 re-reads in tile_spread
+    if (need) spread = tile_spread<TS>(p, env, 0, lane, need, x, y);
+    bool do_reset = false;
+    if (lane == 0) {
+      int r = (flags & F_SCATTER) ? rew : io.cover_in[env];
+      if (p.reward_mode == 0) r += ((!punish && spread) ? 1 : 0) - 1;   // A2C noVis_sim.py:150-152
+      else r += punish ? -1 : (spread ? 1 : 0);                         // DQL noVis_sim.py:141-148
+      const int rem = m.y - ncl;
+      const bool done = rem == 0;                                       // noVis_sim.py:157-166
+      if (p.reward_mode == 0 && done) r += 100;                         // noVis_sim.py:172-173
+      const int t1 = tcount + 1, epret = m.z + r;
+      io.reward_out[(size_t)t * p.N + env] = (float)r;
+      io.done_out[(size_t)t * p.N + env] = done ? 1 : 0;
+      acc.rew += r; acc.cells += ncl; acc.anom += nan;
+      if (done && m.y > 0) { acc.done += 1; acc.len += t1; acc.ret += epret; }
+      do_reset = done && (flags & F_RESET);
+      if (!do_reset) __stcg(p.meta + env, make_int4(t1, rem, epret, m.w));
+    }
+    do_reset = __shfl_sync(FULL, (int)do_reset, 0) != 0;
+    const int episode = __shfl_sync(FULL, m.w, 0);
+    if (do_reset) reset_tile<TS>(p, env, episode + 1, lane, true);
+  } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
+    if (lane == 0) {
+      io.cover_out[env] = rew;
+      if (ncl) p.meta[env].y -= ncl;
+    }
+  }
+  __syncwarp();
+}
+
+template <typename OT>
+__global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int flags = io.flags;
+  const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
+  const bool stepping = (flags & (F_MOVE | F_SCATTER | F_REWARD)) != 0;
+  StatAcc acc;
+  for (int env = blockIdx.x; env < p.N; env += gridDim.x)
+    for (int t = 0; t < io.T; ++t) {
+      if (stepping) {
+        if (warp == 0) step_env_warp(p, io, t, env, lane, acc);
+        __syncthreads();   // warp 0's grid / position updates (L2) are visible to the CTA
+      }
+      if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
+        OT* o = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * p.N * p.obs_per_env);
+        emit_obs_global<OT>(p, env, threadIdx.x, blockDim.x, o);
+        if (stepping && t + 1 < io.T) __syncthreads();   // emission reads precede the next step's clears
+      }
+    }
+
+  if (io.stats && (flags & F_REWARD)) {   // only warp 0 accumulated
+    if (warp == 0) {
+      long long v[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(FULL, v[k], o);
+        if (lane == 0 && v[k] != 0) atomicAdd(io.stats + 2 + k, (unsigned long long)v[k]);
+      }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      atomicAdd(io.stats + 0, (unsigned long long)((long long)p.N * io.T));
+      atomicAdd(io.stats + 1, (unsigned long long)((long long)p.N * p.D * io.T));
+    }
+  }
+}
+
+}  // namespace swarm

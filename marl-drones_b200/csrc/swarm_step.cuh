@@ -15,6 +15,22 @@
 
 namespace swarm {
 
+constexpr int F_RESET = 16;   // auto-reset on done inside the step (A2C/envs.py:22-26)
+
+struct StepIO {
+  const void* actions;     // [T][N][D] of act_dtype
+  int act_dtype;
+  void* obs_out;           // [T][N][obs_per_env] (or one step when obs_last_only), may be null
+  int obs_last_only;
+  float* reward_out;       // [T][N]
+  uint8_t* done_out;       // [T][N]
+  const int* cover_in;     // staged reward: coverage reward per env
+  int* cover_out;          // staged scatter
+  unsigned long long* stats;   // int64[8] accumulated, may be null
+  int T;
+  int flags;
+};
+
 __device__ __forceinline__ int load_action(const void* a, int dt, long long idx) {
   if (dt == 0) return (int)((const uint8_t*)a)[idx];
   if (dt == 1) return ((const int*)a)[idx];
@@ -76,7 +92,7 @@ __device__ __forceinline__ void reset_tile(const DevParams& p, int env, int epis
 template <int TS>
 __device__ __forceinline__ bool tile_spread(const DevParams& p, int env, int tile, int tl, bool need, float x, float y) {
   const int D = p.D;
-  const double thr2 = p.spread_thr * p.spread_thr;
+  const double thr2 = p.spread2_thr;   // sqrt(d2) > row_count // n_drones  <=>  d2 > spread2_thr
   const unsigned tm = (TS == 32) ? FULL : (((1u << TS) - 1u) << (tile * TS));
   bool found = false;
   if (D <= TS) {
@@ -113,7 +129,9 @@ __device__ __forceinline__ bool tile_spread(const DevParams& p, int env, int til
 // ------------------------------------------------------------------------------------------------ scatter (generic cd)
 // Sequential _det_collision for collision_dist > 0.5 (later drones see earlier clears, noVis_sim.py:82): the tile
 // leader walks the drones in index order over the bounded window |g - pos| <= ceil(cd)+1.
-__device__ __forceinline__ void scatter_sequential(const DevParams& p, int env, uint32_t* g, int& rew, int& ncl, int& nan) {
+// `sg` (may be null) is the shared-memory copy of the env's packed grid kept by the staged kernel: reads come from it and
+// every clear is written to both copies (only this thread touches this env's words during the launch).
+__device__ __forceinline__ void scatter_sequential(const DevParams& p, int env, uint32_t* g, uint32_t* sg, int& rew, int& ncl, int& nan) {
   int16_t* wt = p.has_wait ? p.wait + (size_t)env * p.RC : nullptr;
   for (int d = 0; d < p.D; ++d) {
     const float2 q = __ldcg(p.pos + (size_t)env * p.D + d);
@@ -124,15 +142,16 @@ __device__ __forceinline__ void scatter_sequential(const DevParams& p, int env, 
     for (int gx = x0; gx <= x1 && !hit; ++gx)
       for (int gy = y0; gy <= y1; ++gy) {
         const double dx = (double)gx - x, dy = (double)gy - y;
-        if (!(sqrt(dx * dx + dy * dy) < p.cd)) continue;
+        if (!(dx * dx + dy * dy < p.cd2_thr)) continue;   // sqrt(d2) < cd (noVis_sim.py:81)
         const int cell = gy * p.R + gx, sh = (cell & 15) * 2;
-        const uint32_t word = ld_grid(g + (cell >> 4));
+        const uint32_t word = sg ? sg[cell >> 4] : ld_grid(g + (cell >> 4));
         const uint32_t code = (word >> sh) & 3u;
         if (!code) continue;
         if (wt && wt[cell] > 0) {
           wt[cell] -= 1;
         } else {
           st_grid(g + (cell >> 4), word & ~(3u << sh));
+          if (sg) sg[cell >> 4] = word & ~(3u << sh);
           rew += 10 + (code == 2u ? 20 : 0);
           ncl += 1;
           nan += (code == 2u);
