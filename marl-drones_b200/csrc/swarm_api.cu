@@ -16,7 +16,7 @@ struct SwarmEnv {
   int ts;                 // tile size (lanes per env) of the staged warp kernel
   int staged;             // 1: swarm_warp.cuh kernel (grid staged in shared memory), 0: swarm_cta.cuh (one CTA per env)
   int wpb;                // warps per block of the staged kernel
-  int smem_ok;            // dynamic shared-memory limit raised for this handle's kernel instantiation
+  int resident[2];        // resident CTAs of the staged kernel on this device ([0] generic, [1] FAST instantiation); 0 = not yet queried
   int sm_count;
   long long launches;
   unsigned long long* stats_dev;   // int64[8] internal statistics
@@ -94,11 +94,6 @@ static int pick_tile(const SwarmConfig* c, int env_words, int sms, int* warp_sme
     }
   }
   return 0;
-}
-
-template <typename K>
-static cudaError_t allow_smem(K kernel, int bytes) {
-  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
 
 static int use_device(const SwarmEnv* e) {
@@ -251,21 +246,35 @@ extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* 
 }
 
 // ------------------------------------------------------------------------------------------------ launches
-template <int TS, typename OT>
-static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st, int blocks, int smem) {
-  const DevParams& p = e->p;
-  cudaError_t err;
-  if (p.obs_mode == SWARM_OBS_FULL) {
-    if (!e->smem_ok && (err = allow_smem(step_warp_kernel<TS, OT, 0, 0>, smem)) != cudaSuccess) return err;
-    step_warp_kernel<TS, OT, 0, 0><<<blocks, e->wpb * 32, smem, st>>>(p, io);
-  } else if (p.W == 5) {
-    if (!e->smem_ok && (err = allow_smem(step_warp_kernel<TS, OT, 1, 5>, smem)) != cudaSuccess) return err;
-    step_warp_kernel<TS, OT, 1, 5><<<blocks, e->wpb * 32, smem, st>>>(p, io);
-  } else {
-    if (!e->smem_ok && (err = allow_smem(step_warp_kernel<TS, OT, 1, 0>, smem)) != cudaSuccess) return err;
-    step_warp_kernel<TS, OT, 1, 0><<<blocks, e->wpb * 32, smem, st>>>(p, io);
+// One instantiation of the staged kernel: raises its dynamic shared-memory limit once per handle, sizes the persistent
+// grid from the occupancy calculator (resident CTAs only) and launches.
+template <int TS, typename OT, int MODE, int WC, bool FAST>
+static cudaError_t launch_warp_inst(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks_needed, int smem) {
+  auto kernel = step_warp_kernel<TS, OT, MODE, WC, FAST>;
+  int& resident = e->resident[FAST ? 1 : 0];
+  if (resident == 0) {
+    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (err != cudaSuccess) return err;
+    int per_sm = 0;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, e->wpb * 32, smem);
+    if (err != cudaSuccess) return err;
+    resident = (per_sm > 0 ? per_sm : 1) * e->sm_count;
   }
+  const long long blocks = blocks_needed < resident ? blocks_needed : resident;
+  kernel<<<(int)blocks, e->wpb * 32, smem, st>>>(e->p, io);
   return cudaSuccess;
+}
+
+template <int TS, typename OT>
+static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks, int smem) {
+  const DevParams& p = e->p;
+  // FAST: every stage in one pass, uint8 actions, cd <= 0.5, no dwell — the swarm_step / swarm_rollout production path
+  const bool fast = (io.flags & F_ALL) == F_ALL && io.act_dtype == SWARM_ACT_U8 && p.cd_fast && !p.has_wait;
+  if (p.obs_mode == SWARM_OBS_FULL)
+    return fast ? launch_warp_inst<TS, OT, 0, 0, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, OT, 0, 0, false>(e, io, st, blocks, smem);
+  if (p.W == 5)
+    return fast ? launch_warp_inst<TS, OT, 1, 5, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, OT, 1, 5, false>(e, io, st, blocks, smem);
+  return fast ? launch_warp_inst<TS, OT, 1, 0, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, OT, 1, 0, false>(e, io, st, blocks, smem);
 }
 
 template <typename OT>
@@ -275,15 +284,13 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st
   if (e->staged) {
     const int epw = 32 / e->ts;
     const long long ngroups = ((long long)p.N + epw - 1) / epw;
-    long long blocks = (ngroups + e->wpb - 1) / e->wpb;
-    const long long cap = (long long)e->sm_count * 64;     // more CTAs than fit: the hardware scheduler balances the tail
-    if (blocks > cap) blocks = cap;
+    const long long blocks = (ngroups + e->wpb - 1) / e->wpb;
     const int smem = e->wpb * p.warp_smem;
     switch (e->ts) {
-      case 4: err = launch_warp_ts<4, OT>(e, io, st, (int)blocks, smem); break;
-      case 8: err = launch_warp_ts<8, OT>(e, io, st, (int)blocks, smem); break;
-      case 16: err = launch_warp_ts<16, OT>(e, io, st, (int)blocks, smem); break;
-      default: err = launch_warp_ts<32, OT>(e, io, st, (int)blocks, smem); break;
+      case 4: err = launch_warp_ts<4, OT>(e, io, st, blocks, smem); break;
+      case 8: err = launch_warp_ts<8, OT>(e, io, st, blocks, smem); break;
+      case 16: err = launch_warp_ts<16, OT>(e, io, st, blocks, smem); break;
+      default: err = launch_warp_ts<32, OT>(e, io, st, blocks, smem); break;
     }
   } else {
     long long blocks = p.N;
@@ -292,7 +299,6 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st
     step_cta_kernel<OT><<<(int)blocks, 256, 0, st>>>(p, io);
   }
   e->launches++;
-  if (err == cudaSuccess) e->smem_ok = 1;
   return err;
 }
 

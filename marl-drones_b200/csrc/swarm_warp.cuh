@@ -19,6 +19,10 @@
 #include "swarm_emit.cuh"
 #include "swarm_step.cuh"
 
+#ifndef SWARM_MINB
+#define SWARM_MINB 4   // resident CTAs per SM the staged kernel is compiled for (register cap 65536 / (256 * SWARM_MINB))
+#endif
+
 namespace swarm {
 
 // init_env (A2C/noVis_sim.py:36-63) for the env of this tile, built in shared memory and copied out to HBM.
@@ -131,12 +135,26 @@ __device__ __forceinline__ void emit_full_smem(const DevParams& p, const ObsCvt<
 
 // ------------------------------------------------------------------------------------------------ the kernel
 // MODE: 0 FULL obs, 1 WINDOW obs.  WC: compile-time window size (5) or 0 = runtime p.W.
-template <int TS, typename OT, int MODE, int WC>
-__global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
+// FAST: the production configuration folded at compile time — all four stages in one pass (swarm_step / swarm_rollout),
+//       uint8 actions, collision_dist <= 0.5, no dwell counters.  FAST = false keeps every switch at run time (stage entry
+//       points, int32/int64 actions, cd > 0.5, dwell).
+// The grid is persistent (resident CTAs only); a warp strides over its groups, so the prologue and the statistics epilogue
+// are paid once per warp, and the int64[8] statistics cost six RED.ADD per CTA.
+template <int TS, typename OT, int MODE, int WC, bool FAST>
+__global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
   constexpr int EPW = 32 / TS;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t bars[8];
+  __shared__ unsigned long long s_stats[6];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int flags = FAST ? (F_ALL | (io.flags & F_RESET)) : io.flags;
+  const bool cd_fast = FAST ? true : (p.cd_fast != 0);
+  const bool has_wait = FAST ? false : (p.has_wait != 0);
+  const bool want_stats = io.stats != nullptr && (flags & F_REWARD);
+  if (want_stats) {
+    if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
+    __syncthreads();
+  }
   unsigned char* wbase = smem_raw + (size_t)wib * p.warp_smem;
   OT* stage = reinterpret_cast<OT*>(wbase);                                   // [EPW][D][W*W] obs staging (WINDOW)
   uint32_t* sgrid = reinterpret_cast<uint32_t*>(wbase + p.stage_bytes);       // [EPW][env_words] packed grids
@@ -148,38 +166,42 @@ __global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ 
   __syncwarp();
   uint32_t phase = 0;
   const int tile = lane / TS, tl = lane % TS, lead = tile * TS;
-  const int D = p.D, flags = io.flags;
-  const int ngroups = (p.N + EPW - 1) / EPW;
+  const int D = p.D, N = p.N, env_words = p.env_words;
+  const int ngroups = (N + EPW - 1) / EPW;
   const int gw = blockIdx.x * wpb + wib, nw = gridDim.x * wpb;
   const ObsCvt<OT> cvt(p);
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
+  const int WW = MODE == 1 ? (WC ? WC : p.W) * (WC ? WC : p.W) : 1;
+  uint32_t* const sg = sgrid + tile * env_words;
+  OT* const my_stage = stage + (tile * D + tl) * WW;
   StatAcc acc;
 
   for (int grp = gw; grp < ngroups; grp += nw) {
-    const int env0 = grp * EPW, nenv = min(EPW, p.N - env0);
+    const int env0 = grp * EPW, nenv = min(EPW, N - env0);
     const bool valid = tile < nenv;
     const int env = valid ? env0 + tile : env0;
     const bool active = valid && tl < D;
-    uint32_t* sg = sgrid + tile * p.env_words;
-    uint32_t* gg = p.grid + (size_t)env * p.env_words;
+    uint32_t* const gg = p.grid + (size_t)env * env_words;
 
     // (a) stage the group's packed grids: one TMA bulk copy, completion on the warp's mbarrier
     if (lane == 0) {
       bulk_wait_read0();   // the previous group's obs bulk store no longer reads `stage`
-      const uint32_t bytes = (uint32_t)nenv * (uint32_t)p.env_words * 4u;
+      const uint32_t bytes = (uint32_t)nenv * (uint32_t)env_words * 4u;
       mbar_expect_tx(bar, bytes);
-      bulk_g2s(sgrid, p.grid + (size_t)env0 * p.env_words, bytes, bar);
+      bulk_g2s(sgrid, p.grid + (size_t)env0 * env_words, bytes, bar);
     }
+    float2* const pp = p.pos + (size_t)env * D + (active ? tl : 0);
+    size_t aidx = (size_t)env * D + tl;                 // action index, advanced by N*D per step
+    size_t ridx = (size_t)env;                          // reward / done index, advanced by N per step
 
-    for (int t = 0; t < io.T; ++t) {
+    for (int t = 0; t < io.T; ++t, aidx += (size_t)N * D, ridx += N) {
       // ---- loads for this step, all in flight together with the bulk copy
       float2 q = make_float2(0.f, 0.f);
       int a = 0;
       int4 m = make_int4(0, 0, 0, 0);
-      float2* pp = p.pos + (size_t)env * D + (active ? tl : 0);
       if (active) {
         q = __ldcg(pp);
-        if (flags & F_MOVE) a = load_action(io.actions, io.act_dtype, ((long long)t * p.N + env) * D + tl);
+        if (flags & F_MOVE) a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
       }
       if (valid && tl == 0 && (flags & F_REWARD)) m = __ldcg(p.meta + env);
       if (t == 0) {
@@ -189,27 +211,24 @@ __global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ 
 
       // ---- stage (1): action decode + move + clip (noVis_sim.py:117-135)
       if (active && (flags & F_MOVE)) {
-        if (a == 0) q.y -= p.ss;
-        else if (a == 1) q.x += p.ss;
-        else if (a == 2) q.y += p.ss;
-        else if (a == 3) q.x -= p.ss;
-        else atomicOr(p.err, 1);
-        q.x = fminf(fmaxf(q.x, 0.f), p.xmax);
-        q.y = fminf(fmaxf(q.y, 0.f), p.ymax);
+        const float sx = (a == 1) ? p.ss : ((a == 3) ? -p.ss : 0.f);
+        const float sy = (a == 2) ? p.ss : ((a == 0) ? -p.ss : 0.f);
+        if ((unsigned)a > 3u) atomicOr(p.err, 1);
+        q.x = fminf(fmaxf(q.x + sx, 0.f), p.xmax);
+        q.y = fminf(fmaxf(q.y + sy, 0.f), p.ymax);
         __stcg(pp, q);
       }
+      const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);   // nearest lattice cell = window centre
 
       // ---- stage (2): coverage scatter on the shared-memory grid, conflicts resolved with a warp match
       int rew = 0, ncl = 0, nan = 0;
       if (flags & F_SCATTER) {
-        if (p.cd_fast) {   // cd <= 0.5: the only candidate is the nearest lattice cell
+        if (cd_fast) {   // cd <= 0.5: the only candidate is the nearest lattice cell
           bool cand = false;
-          int cell = 0;
+          const int cell = cy * p.R + cx;
           if (active) {
-            const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
-            const double dx = (double)cx - (double)q.x, dy = (double)cy - (double)q.y;
+            const double dx = (double)((float)cx - q.x), dy = (double)((float)cy - q.y);   // exact differences
             cand = dx * dx + dy * dy < p.cd2_thr;     // sqrt(d2) < collision_dist (noVis_sim.py:81)
-            cell = cy * p.R + cx;
           }
           // drones of one env on one cell form a match group; its lowest lane resolves the conflict for all of them
           const unsigned key = cand ? (((unsigned)tile << 24) | (unsigned)cell) : (0x80000000u | (unsigned)lane);
@@ -219,7 +238,7 @@ __global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ 
             const uint32_t code = (sg[cell >> 4] >> sh) & 3u;
             if (code) {
               bool clear = true;
-              if (p.has_wait) {   // dwell (App. B.2): k drones in index order, each decrements or (at 0) maps
+              if (has_wait) {   // dwell (App. B.2): k drones in index order, each decrements or (at 0) maps
                 const int k = __popc(mm);
                 int16_t* w = p.wait + (size_t)env * p.RC + cell;
                 const int wv = *w;
@@ -262,16 +281,20 @@ __global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ 
           const bool done = rem == 0;                                       // noVis_sim.py:157-166
           if (p.reward_mode == 0 && done) r += 100;                         // noVis_sim.py:172-173
           const int t1 = tcount + 1, epret = m.z + r;
-          io.reward_out[(size_t)t * p.N + env] = (float)r;
-          io.done_out[(size_t)t * p.N + env] = done ? 1 : 0;
+          io.reward_out[ridx] = (float)r;
+          io.done_out[ridx] = done ? 1 : 0;
           acc.rew += r; acc.cells += ncl; acc.anom += nan;
           if (done && m.y > 0) { acc.done += 1; acc.len += t1; acc.ret += epret; }
           do_reset = done && (flags & F_RESET);
           if (!do_reset) __stcg(p.meta + env, make_int4(t1, rem, epret, m.w));
         }
-        do_reset = __shfl_sync(FULL, (int)do_reset, lead) != 0;
-        const int episode = __shfl_sync(FULL, m.w, lead);
-        if (__any_sync(FULL, do_reset)) reset_tile_smem<TS>(p, env, episode + 1, tl, do_reset, sg, q);
+        if (flags & F_RESET) {
+          do_reset = __shfl_sync(FULL, (int)do_reset, lead) != 0;
+          if (__any_sync(FULL, do_reset)) {   // rare: an episode finished
+            const int episode = __shfl_sync(FULL, m.w, lead);
+            reset_tile_smem<TS>(p, env, episode + 1, tl, do_reset, sg, q);
+          }
+        }
       } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
         if (valid && tl == 0) {
           io.cover_out[env] = rew;
@@ -281,16 +304,15 @@ __global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ 
 
       // ---- stage (4): observation emission
       if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
-        OT* obase = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * p.N * p.obs_per_env);
+        OT* obase = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * N * p.obs_per_env);
         if (MODE == 0) {
           emit_full_smem<OT>(p, cvt, sgrid, nenv, lane, obase + (size_t)env0 * p.RC);
         } else {
-          const int WW = (WC ? WC : p.W) * (WC ? WC : p.W);
           if (t > 0) {   // the previous step's bulk store must have drained `stage`
             if (lane == 0) bulk_wait_read0();
             __syncwarp();
           }
-          if (active) build_window<WC, OT>(p, cvt, sg, q, stage + (size_t)(tile * D + tl) * WW);
+          if (active) build_window<WC, OT>(p, cvt, sg, q, my_stage);
           fence_proxy_async();   // generic-proxy writes to `stage` ordered before the async-proxy read below
           __syncwarp();
           const int n = nenv * D * WW;
@@ -313,22 +335,18 @@ __global__ void __launch_bounds__(256) step_warp_kernel(const __grid_constant__ 
   }
   if (lane == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
 
-  if (io.stats && (flags & F_REWARD)) {
-    __shared__ unsigned long long s[6];
-    if (threadIdx.x < 6) s[threadIdx.x] = 0ull;
-    __syncthreads();
-    long long v[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
+  if (want_stats) {   // only tile leaders accumulated; zero entries are skipped
+    if (tl == 0) {
+      const long long v[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(FULL, v[k], o);
-      if (lane == 0 && v[k] != 0) atomicAdd(&s[k], (unsigned long long)v[k]);
+      for (int k = 0; k < 6; ++k)
+        if (v[k] != 0) atomicAdd(&s_stats[k], (unsigned long long)v[k]);
     }
     __syncthreads();
-    if (threadIdx.x < 6 && s[threadIdx.x] != 0ull) atomicAdd(io.stats + 2 + threadIdx.x, s[threadIdx.x]);
+    if (threadIdx.x < 6 && s_stats[threadIdx.x] != 0ull) atomicAdd(io.stats + 2 + threadIdx.x, s_stats[threadIdx.x]);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-      atomicAdd(io.stats + 0, (unsigned long long)((long long)p.N * io.T));
-      atomicAdd(io.stats + 1, (unsigned long long)((long long)p.N * p.D * io.T));
+      atomicAdd(io.stats + 0, (unsigned long long)((long long)N * io.T));
+      atomicAdd(io.stats + 1, (unsigned long long)((long long)N * D * io.T));
     }
   }
 }

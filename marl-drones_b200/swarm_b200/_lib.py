@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _PKG_ROOT = os.path.dirname(_HERE)                      # marl-drones_b200/
 _REPO = os.path.dirname(_PKG_ROOT)
 CSRC = os.path.join(_PKG_ROOT, "csrc")
-SO_PATH = os.path.join(_HERE, "libswarm_b200.so")
+SO_PATH = os.environ.get("SWARM_B200_SO") or os.path.join(_HERE, "libswarm_b200.so")   # override: kernel-variant experiments
 HEADER = os.path.join(_REPO, "include", "swarm_b200.h")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -51,7 +51,7 @@ def build(force=False, verbose=False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     if not os.path.exists(nvcc):
         nvcc = "nvcc"
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", SO_PATH, os.path.join(CSRC, "swarm_api.cu")]
+    cmd = [nvcc] + NVCC_FLAGS + os.environ.get("SWARM_NVCC_EXTRA", "").split() + ["-o", SO_PATH, os.path.join(CSRC, "swarm_api.cu")]
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)
