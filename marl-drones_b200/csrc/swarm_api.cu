@@ -67,7 +67,7 @@ extern "C" int swarm_device_count(void) {
 }
 
 // ---- kernel selection ------------------------------------------------------------------------------------------------
-constexpr int kWarpSmemMax = 12 * 1024;     // per-warp shared-memory slice the staged kernel may use
+constexpr int kWarpSmemMax = 20 * 1024;     // per-warp shared-memory slice the staged kernel may use
 constexpr int kCtaSmemMax = 200 * 1024;
 
 static int stage_bytes_for(const SwarmConfig* c, int epw) {
@@ -76,9 +76,12 @@ static int stage_bytes_for(const SwarmConfig* c, int epw) {
   return (int)((b + 15) / 16 * 16);
 }
 
+static int align16(long long v) { return (int)((v + 15) / 16 * 16); }
+
 // Smallest power-of-two tile >= D (min 4), widened while the batch would give too few warps to fill the GPU.
-// Returns 0 when the shape does not fit the staged kernel (D > 32 or the per-warp slice is too large).
-static int pick_tile(const SwarmConfig* c, int env_words, int sms, int* warp_smem_out, int* stage_out) {
+// Returns 0 when the shape does not fit the staged kernel (D > 32 or the per-warp slice is too large); otherwise fills the
+// per-warp shared-memory carve-up in `p`.
+static int pick_tile(const SwarmConfig* c, int sms, DevParams* p) {
   if (c->n_drones > 32) return 0;
   int ts = 4;
   while (ts < c->n_drones) ts <<= 1;
@@ -86,10 +89,17 @@ static int pick_tile(const SwarmConfig* c, int env_words, int sms, int* warp_sme
   for (; ts <= 32; ts <<= 1) {
     const int epw = 32 / ts;
     const int stage = stage_bytes_for(c, epw);
-    const long long ws = (long long)stage + (long long)epw * env_words * 4 + 16;
+    const int gridb = epw * p->env_words * 4;
+    const int posb = align16((long long)epw * c->n_drones * 8), metab = epw * 16, actb = align16((long long)epw * c->n_drones);
+    const long long in_bytes = (long long)gridb + posb + metab + actb;
+    const long long ws = (long long)stage + 2 * in_bytes + 16;
     if (ws <= kWarpSmemMax) {
-      *warp_smem_out = (int)ws;
-      *stage_out = stage;
+      p->stage_bytes = stage;
+      p->in_bytes = (int)in_bytes;
+      p->off_pos = gridb;
+      p->off_meta = gridb + posb;
+      p->off_act = gridb + posb + metab;
+      p->warp_smem = (int)ws;
       return ts;
     }
   }
@@ -167,11 +177,19 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
     while (z > 0.0 && std::sqrt(z) > p.spread_thr) z = std::nextafter(z, -INFINITY);
     p.spread2_thr = z;                               // largest z with sqrt(z) <= row_count // n_drones
   }
-  e->ts = pick_tile(c, p.env_words, sms, &p.warp_smem, &p.stage_bytes);
+  e->ts = pick_tile(c, sms, &p);
   e->staged = e->ts != 0;
   if (!e->staged) e->ts = 32;
-  e->wpb = 8;
-  while (e->wpb > 1 && (long long)e->wpb * p.warp_smem > kCtaSmemMax / 2) e->wpb >>= 1;   // keep >= 2 CTAs per SM
+  {   // warps per CTA: the choice that packs most warps into an SM's 227 KB (ties -> larger CTAs), at most 32 warps (registers)
+    int best = 0;
+    e->wpb = 8;
+    for (int w = 8; w >= 2; w >>= 1) {
+      long long ctas = (227 * 1024) / ((long long)w * p.warp_smem + 1024 + 4400);
+      long long warps = ctas * w;
+      if (warps > 32) warps = 32;
+      if (warps > best) { best = (int)warps; e->wpb = w; }
+    }
+  }
   p.nq_magic = RC >= 4 ? (uint32_t)(((1ull << 32) + (uint64_t)(RC / 4) - 1) / (uint64_t)(RC / 4)) : 0u;
   p.seed_lo = (uint32_t)c->seed; p.seed_hi = (uint32_t)(c->seed >> 32);
   p.env_id_base = c->env_id_base;

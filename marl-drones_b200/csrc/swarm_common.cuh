@@ -35,7 +35,9 @@ struct DevParams {
   double spread2_thr; // largest double z with sqrt(z) <= spread_thr: sqrt(d2) > thr <=> d2 > spread2_thr
   // warp-autonomous staged kernel (swarm_warp.cuh): per-warp shared-memory carve-up, bytes
   int stage_bytes;    // obs staging (WINDOW mode), multiple of 16, >= 16
-  int warp_smem;      // stage_bytes + EPW*env_words*4 + 16
+  int in_bytes;       // one input buffer: [grid EPW*env_words*4][pos EPW*D*8][meta EPW*16][actions EPW*D], each 16 B aligned
+  int off_pos, off_meta, off_act;   // byte offsets inside an input buffer
+  int warp_smem;      // stage_bytes + 2 * in_bytes + 16
   uint32_t nq_magic;  // ceil(2^32 / (RC/4)) for the FULL-mode vector -> (env, quad) split
   uint32_t seed_lo, seed_hi;
   long long env_id_base;

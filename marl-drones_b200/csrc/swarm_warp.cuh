@@ -3,15 +3,15 @@
 //
 // One warp owns EPW = 32/TS consecutive envs (a "group"); a tile of TS lanes serves one env, one lane per drone.
 // Per group the warp
-//   (a) pulls the group's packed grids (EPW * env_words * 4 bytes, contiguous in HBM) into ITS OWN slice of shared memory
-//       with one TMA bulk copy (cp.async.bulk, mbarrier completion) while positions / actions / meta loads are in flight,
-//       so the whole step costs ONE DRAM round trip;
+//   (a) receives the group's inputs — packed grids (EPW * env_words * 4 bytes, contiguous in HBM), positions, meta and
+//       actions — in ITS OWN slice of shared memory through TMA bulk copies (cp.async.bulk, one mbarrier per buffer),
+//       requested one group ahead into a double buffer, so HBM latency overlaps the previous group's arithmetic;
 //   (b) runs stages (1)-(3) on the shared-memory copy (clears are written through to HBM with RED.AND);
 //   (c) WINDOW obs: every lane gathers its drone's W x W window from shared memory into a staging slice (bank-conflict
 //       free: lane stride W*W words), and one TMA bulk store streams the group's [EPW][D][W*W] block to the obs tensor;
 //       FULL obs: the warp expands the 2-bit grid straight from shared memory with 128-bit streaming stores.
-// There is no __syncthreads anywhere: warps drift through load / compute / store phases independently, which is what
-// keeps HBM busy.  T > 1 (swarm_rollout) keeps the grid in shared memory across steps.
+// There is no __syncthreads in the group loop: warps run load / compute / store independently.  T > 1 (swarm_rollout)
+// keeps grid, positions and meta on chip across steps.
 //
 // Reference lines per stage: see swarm_step.cuh.
 #pragma once
@@ -20,7 +20,7 @@
 #include "swarm_step.cuh"
 
 #ifndef SWARM_MINB
-#define SWARM_MINB 4   // resident CTAs per SM the staged kernel is compiled for (register cap 65536 / (256 * SWARM_MINB))
+#define SWARM_MINB 3   // resident CTAs per SM the staged kernel is compiled for (register cap 65536 / (256 * SWARM_MINB))
 #endif
 
 namespace swarm {
@@ -77,8 +77,11 @@ __device__ __forceinline__ void reset_tile_smem(const DevParams& p, int env, int
 // st[0 .. W*W).  For W <= 15 a window row is one funnel-shifted 32-bit field (16 cells) of the 2-bit stream; cells that
 // belong to out-of-range columns are forced to the pad code, which also covers the neighbouring-row / out-of-buffer bits
 // such a field can contain (the buffer has readable slack on both sides).
+// float obs: `lut4` (shared, 256 x float4) maps a byte of four 2-bit codes to its four float values, so a row costs one
+// LDS.128 per four cells instead of per-cell bit twiddling.
 template <int WC, typename OT>
-__device__ __forceinline__ void build_window(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* sg, float2 q, OT* st) {
+__device__ __forceinline__ void build_window(const DevParams& p, const ObsCvt<OT>& cvt, const float4* lut4, const uint32_t* sg,
+                                             float2 q, OT* st) {
   const int W = WC ? WC : p.W;
   const int h = (W - 1) >> 1;
   const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
@@ -96,8 +99,28 @@ __device__ __forceinline__ void build_window(const DevParams& p, const ObsCvt<OT
         const int wi = s0 >> 4;
         field = __funnelshift_r(sg[wi], sg[wi + 1], (s0 & 15) * 2) | colpad;
       }
+      if constexpr (sizeof(OT) == 4) {
+        float* o = reinterpret_cast<float*>(st) + b * W;
 #pragma unroll
-      for (int a = 0; a < W; ++a) st[b * W + a] = cvt.sel(field, a);
+        for (int a = 0; a < W; a += 4) {
+          const char* e = reinterpret_cast<const char*>(lut4) + (((a ? (field >> (2 * a)) : field) & 0xffu) << 4);
+          if (a + 4 <= W) {
+            const float4 v = *reinterpret_cast<const float4*>(e);
+            o[a] = v.x; o[a + 1] = v.y; o[a + 2] = v.z; o[a + 3] = v.w;
+          } else if (a + 3 == W) {
+            const float2 v = *reinterpret_cast<const float2*>(e);
+            o[a] = v.x; o[a + 1] = v.y; o[a + 2] = reinterpret_cast<const float*>(e)[2];
+          } else if (a + 2 == W) {
+            const float2 v = *reinterpret_cast<const float2*>(e);
+            o[a] = v.x; o[a + 1] = v.y;
+          } else {
+            o[a] = *reinterpret_cast<const float*>(e);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int a = 0; a < W; ++a) st[b * W + a] = cvt.sel(field, a);
+      }
     }
   } else {
     for (int b = 0; b < W; ++b)
@@ -138,97 +161,129 @@ __device__ __forceinline__ void emit_full_smem(const DevParams& p, const ObsCvt<
 // FAST: the production configuration folded at compile time — all four stages in one pass (swarm_step / swarm_rollout),
 //       uint8 actions, collision_dist <= 0.5, no dwell counters.  FAST = false keeps every switch at run time (stage entry
 //       points, int32/int64 actions, cd > 0.5, dwell).
-// The grid is persistent (resident CTAs only); a warp strides over its groups, so the prologue and the statistics epilogue
-// are paid once per warp, and the int64[8] statistics cost six RED.ADD per CTA.
+//
+// Software pipeline: a warp's inputs for group g+1 (packed grids, positions, meta, actions — four TMA bulk copies on one
+// mbarrier, into the other half of a double buffer) are requested BEFORE it computes group g, so HBM latency overlaps the
+// arithmetic even when every warp of the GPU runs in lock step.  The copies need no registers.  The grid is persistent
+// (resident CTAs only): prologue, LUT build and the statistics epilogue are paid once per warp, and the int64[8]
+// statistics cost six RED.ADD per CTA.
 template <int TS, typename OT, int MODE, int WC, bool FAST>
 __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
   constexpr int EPW = 32 / TS;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ uint64_t bars[8];
+  __shared__ uint64_t bars[8][2];
   __shared__ unsigned long long s_stats[6];
+  __shared__ float4 lut4[(MODE == 1 && sizeof(OT) == 4) ? 256 : 1];   // byte of four codes -> four floats (WINDOW, float obs)
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   const int flags = FAST ? (F_ALL | (io.flags & F_RESET)) : io.flags;
   const bool cd_fast = FAST ? true : (p.cd_fast != 0);
   const bool has_wait = FAST ? false : (p.has_wait != 0);
   const bool want_stats = io.stats != nullptr && (flags & F_REWARD);
-  if (want_stats) {
-    if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
-    __syncthreads();
+  const ObsCvt<OT> cvt(p);
+  if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
+  if constexpr (MODE == 1 && sizeof(OT) == 4) {
+    for (int b = threadIdx.x; b < 256; b += blockDim.x) lut4[b] = make_float4(cvt.sel(b, 0), cvt.sel(b, 1), cvt.sel(b, 2), cvt.sel(b, 3));
   }
-  unsigned char* wbase = smem_raw + (size_t)wib * p.warp_smem;
-  OT* stage = reinterpret_cast<OT*>(wbase);                                   // [EPW][D][W*W] obs staging (WINDOW)
-  uint32_t* sgrid = reinterpret_cast<uint32_t*>(wbase + p.stage_bytes);       // [EPW][env_words] packed grids
-  uint64_t* bar = &bars[wib];
+  __syncthreads();
+  unsigned char* const wbase = smem_raw + (size_t)wib * p.warp_smem;
+  OT* const stage = reinterpret_cast<OT*>(wbase);                 // [EPW][D][W*W] obs staging (WINDOW)
+  unsigned char* const inbuf0 = wbase + p.stage_bytes;            // two input buffers of p.in_bytes each
   if (lane == 0) {
-    mbar_init(bar, 1);
+    mbar_init(&bars[wib][0], 1);
+    mbar_init(&bars[wib][1], 1);
     fence_mbar_init();
   }
   __syncwarp();
-  uint32_t phase = 0;
   const int tile = lane / TS, tl = lane % TS, lead = tile * TS;
   const int D = p.D, N = p.N, env_words = p.env_words;
   const int ngroups = (N + EPW - 1) / EPW;
   const int gw = blockIdx.x * wpb + wib, nw = gridDim.x * wpb;
-  const ObsCvt<OT> cvt(p);
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
   const int WW = MODE == 1 ? (WC ? WC : p.W) * (WC ? WC : p.W) : 1;
-  uint32_t* const sg = sgrid + tile * env_words;
   OT* const my_stage = stage + (tile * D + tl) * WW;
-  StatAcc acc;
+  // which per-group arrays may ride the bulk copy (size and address multiples of 16 B; the grid and meta always do)
+  const bool act_tma_ok = (flags & F_MOVE) && (FAST || io.act_dtype == 0) && (((uintptr_t)io.actions) & 15) == 0;
+  const bool meta_tma = (flags & F_REWARD) != 0;
+  // statistics accumulators are warp-uniform (REDUX results), so they live in uniform registers
+  long long acc_rew = 0, acc_len = 0, acc_ret = 0;
+  int acc_done = 0, acc_cells = 0, acc_anom = 0;
 
-  for (int grp = gw; grp < ngroups; grp += nw) {
+  // lane 0: request the inputs of group `g` into buffer `b`
+  auto prefetch = [&](int g, int b) {
+    const int e0 = g * EPW, ne = min(EPW, N - e0);
+    unsigned char* in = inbuf0 + b * p.in_bytes;
+    uint64_t* bar = &bars[wib][b];
+    const uint32_t gbytes = (uint32_t)ne * (uint32_t)env_words * 4u, nd = (uint32_t)ne * (uint32_t)D;
+    const bool pos_tma = ((nd * 8u) & 15u) == 0 && (((uint32_t)e0 * (uint32_t)D * 8u) & 15u) == 0;
+    const bool act_tma = act_tma_ok && (nd & 15u) == 0 && (((uint32_t)e0 * (uint32_t)D) & 15u) == 0 && io.T == 1;
+    mbar_expect_tx(bar, gbytes + (pos_tma ? nd * 8u : 0u) + (meta_tma ? (uint32_t)ne * 16u : 0u) + (act_tma ? nd : 0u));
+    bulk_g2s(in, p.grid + (size_t)e0 * env_words, gbytes, bar);
+    if (pos_tma) bulk_g2s(in + p.off_pos, p.pos + (size_t)e0 * D, nd * 8u, bar);
+    if (meta_tma) bulk_g2s(in + p.off_meta, p.meta + e0, (uint32_t)ne * 16u, bar);
+    if (act_tma) bulk_g2s(in + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, nd, bar);
+  };
+
+  uint32_t phases = 0;
+  if (gw < ngroups && lane == 0) prefetch(gw, 0);
+  int it = 0;
+  for (int grp = gw; grp < ngroups; grp += nw, ++it) {
+    const int b = it & 1;
+    unsigned char* const in = inbuf0 + b * p.in_bytes;
+    uint32_t* const sgrid = reinterpret_cast<uint32_t*>(in);
     const int env0 = grp * EPW, nenv = min(EPW, N - env0);
     const bool valid = tile < nenv;
     const int env = valid ? env0 + tile : env0;
     const bool active = valid && tl < D;
+    uint32_t* const sg = sgrid + tile * env_words;
     uint32_t* const gg = p.grid + (size_t)env * env_words;
-
-    // (a) stage the group's packed grids: one TMA bulk copy, completion on the warp's mbarrier
-    if (lane == 0) {
-      bulk_wait_read0();   // the previous group's obs bulk store no longer reads `stage`
-      const uint32_t bytes = (uint32_t)nenv * (uint32_t)env_words * 4u;
-      mbar_expect_tx(bar, bytes);
-      bulk_g2s(sgrid, p.grid + (size_t)env0 * env_words, bytes, bar);
-    }
+    const uint32_t nd = (uint32_t)nenv * (uint32_t)D;
+    const bool pos_tma = ((nd * 8u) & 15u) == 0 && (((uint32_t)env0 * (uint32_t)D * 8u) & 15u) == 0;
+    const bool act_tma = act_tma_ok && (nd & 15u) == 0 && (((uint32_t)env0 * (uint32_t)D) & 15u) == 0 && io.T == 1;
     float2* const pp = p.pos + (size_t)env * D + (active ? tl : 0);
     size_t aidx = (size_t)env * D + tl;                 // action index, advanced by N*D per step
     size_t ridx = (size_t)env;                          // reward / done index, advanced by N per step
 
+    // inputs that did not ride the bulk copy (odd shapes): plain loads, issued before the wait
+    float2 q = make_float2(0.f, 0.f);
+    int a = 0;
+    int4 m = make_int4(0, 0, 0, 0);
+    if (active && !pos_tma) q = __ldcg(pp);
+    if (active && !act_tma && (flags & F_MOVE)) a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
+
+    mbar_wait(&bars[wib][b], (phases >> b) & 1u);
+    phases ^= 1u << b;
+    // the other buffer's readers finished before the fence that ended the previous group: refill it now
+    if (lane == 0 && grp + nw < ngroups) prefetch(grp + nw, b ^ 1);
+    if (active && pos_tma) q = reinterpret_cast<const float2*>(in + p.off_pos)[tile * D + tl];
+    if (active && act_tma) a = (int)in[p.off_act + tile * D + tl];
+    if (valid && tl == 0 && meta_tma) m = reinterpret_cast<const int4*>(in + p.off_meta)[tile];
+
     for (int t = 0; t < io.T; ++t, aidx += (size_t)N * D, ridx += N) {
-      // ---- loads for this step, all in flight together with the bulk copy
-      float2 q = make_float2(0.f, 0.f);
-      int a = 0;
-      int4 m = make_int4(0, 0, 0, 0);
-      if (active) {
-        q = __ldcg(pp);
-        if (flags & F_MOVE) a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
-      }
-      if (valid && tl == 0 && (flags & F_REWARD)) m = __ldcg(p.meta + env);
-      if (t == 0) {
-        mbar_wait(bar, phase);
-        phase ^= 1u;
-      }
+      if (t > 0 && active && (flags & F_MOVE))   // rollout: positions / meta are carried in registers, actions are re-read
+        a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
 
       // ---- stage (1): action decode + move + clip (noVis_sim.py:117-135)
       if (active && (flags & F_MOVE)) {
-        const float sx = (a == 1) ? p.ss : ((a == 3) ? -p.ss : 0.f);
-        const float sy = (a == 2) ? p.ss : ((a == 0) ? -p.ss : 0.f);
+        float sx = (a == 1) ? p.ss : 0.f, sy = (a == 2) ? p.ss : 0.f;   // a=0: y-=ss, 1: x+=ss, 2: y+=ss, 3: x-=ss
+        sx = (a == 3) ? -p.ss : sx;
+        sy = (a == 0) ? -p.ss : sy;
         if ((unsigned)a > 3u) atomicOr(p.err, 1);
         q.x = fminf(fmaxf(q.x + sx, 0.f), p.xmax);
         q.y = fminf(fmaxf(q.y + sy, 0.f), p.ymax);
         __stcg(pp, q);
       }
-      const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);   // nearest lattice cell = window centre
 
       // ---- stage (2): coverage scatter on the shared-memory grid, conflicts resolved with a warp match
       int rew = 0, ncl = 0, nan = 0;
       if (flags & F_SCATTER) {
         if (cd_fast) {   // cd <= 0.5: the only candidate is the nearest lattice cell
           bool cand = false;
-          const int cell = cy * p.R + cx;
+          int cell = 0;
           if (active) {
-            const double dx = (double)((float)cx - q.x), dy = (double)((float)cy - q.y);   // exact differences
+            const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
+            const double dx = (double)((float)cx - q.x), dy = (double)((float)cy - q.y);   // both differences are exact
             cand = dx * dx + dy * dy < p.cd2_thr;     // sqrt(d2) < collision_dist (noVis_sim.py:81)
+            cell = cy * p.R + cx;
           }
           // drones of one env on one cell form a match group; its lowest lane resolves the conflict for all of them
           const unsigned key = cand ? (((unsigned)tile << 24) | (unsigned)cell) : (0x80000000u | (unsigned)lane);
@@ -273,6 +328,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
         bool spread = false;
         if (__any_sync(FULL, need)) spread = tile_spread<TS>(p, env, tile, tl, need, q.x, q.y);
         bool do_reset = false;
+        int s_r = 0, s_cl = 0, s_an = 0, s_len = 0, s_ret = 0;   // this lane's contribution to the statistics
+        bool s_done = false;
         if (valid && tl == 0) {
           int r = (flags & F_SCATTER) ? rew : io.cover_in[env];
           if (p.reward_mode == 0) r += ((!punish && spread) ? 1 : 0) - 1;   // A2C noVis_sim.py:150-152
@@ -283,16 +340,31 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
           const int t1 = tcount + 1, epret = m.z + r;
           io.reward_out[ridx] = (float)r;
           io.done_out[ridx] = done ? 1 : 0;
-          acc.rew += r; acc.cells += ncl; acc.anom += nan;
-          if (done && m.y > 0) { acc.done += 1; acc.len += t1; acc.ret += epret; }
+          s_r = r; s_cl = ncl; s_an = nan;
+          if (done && m.y > 0) { s_done = true; s_len = t1; s_ret = epret; }
           do_reset = done && (flags & F_RESET);
-          if (!do_reset) __stcg(p.meta + env, make_int4(t1, rem, epret, m.w));
+          if (!do_reset) {
+            m = make_int4(t1, rem, epret, m.w);
+            __stcg(p.meta + env, m);
+          } else {
+            m = make_int4(0, p.RC, 0, m.w + 1);   // what reset_tile_smem writes
+          }
+        }
+        if (want_stats) {
+          acc_rew += __reduce_add_sync(FULL, s_r);
+          acc_cells += __reduce_add_sync(FULL, s_cl);
+          acc_anom += __reduce_add_sync(FULL, s_an);
+          if (__any_sync(FULL, s_done)) {   // rare: an episode finished
+            acc_done += __popc(__ballot_sync(FULL, s_done));
+            acc_len += __reduce_add_sync(FULL, s_len);
+            acc_ret += __reduce_add_sync(FULL, s_ret);
+          }
         }
         if (flags & F_RESET) {
           do_reset = __shfl_sync(FULL, (int)do_reset, lead) != 0;
           if (__any_sync(FULL, do_reset)) {   // rare: an episode finished
-            const int episode = __shfl_sync(FULL, m.w, lead);
-            reset_tile_smem<TS>(p, env, episode + 1, tl, do_reset, sg, q);
+            const int episode = __shfl_sync(FULL, m.w, lead);   // already the new episode index where do_reset
+            reset_tile_smem<TS>(p, env, episode, tl, do_reset, sg, q);
           }
         }
       } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
@@ -308,11 +380,9 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
         if (MODE == 0) {
           emit_full_smem<OT>(p, cvt, sgrid, nenv, lane, obase + (size_t)env0 * p.RC);
         } else {
-          if (t > 0) {   // the previous step's bulk store must have drained `stage`
-            if (lane == 0) bulk_wait_read0();
-            __syncwarp();
-          }
-          if (active) build_window<WC, OT>(p, cvt, sg, q, my_stage);
+          if (lane == 0) bulk_wait_read0();   // the previous bulk store has drained `stage` (long ago)
+          __syncwarp();
+          if (active) build_window<WC, OT>(p, cvt, lut4, sg, q, my_stage);
           fence_proxy_async();   // generic-proxy writes to `stage` ordered before the async-proxy read below
           __syncwarp();
           const int n = nenv * D * WW;
@@ -330,14 +400,14 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
       }
       __syncwarp();
     }
-    fence_proxy_async();   // this group's generic accesses to sgrid/stage precede the next group's bulk copy
+    fence_proxy_async();   // this group's generic accesses to its input buffer precede the bulk copy that refills it
     __syncwarp();
   }
   if (lane == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
 
-  if (want_stats) {   // only tile leaders accumulated; zero entries are skipped
-    if (tl == 0) {
-      const long long v[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
+  if (want_stats) {   // one lane per warp adds the warp's (uniform) totals; zero entries are skipped
+    if (lane == 0) {
+      const long long v[6] = {acc_rew, (long long)acc_done, acc_len, acc_ret, (long long)acc_cells, (long long)acc_anom};
 #pragma unroll
       for (int k = 0; k < 6; ++k)
         if (v[k] != 0) atomicAdd(&s_stats[k], (unsigned long long)v[k]);
