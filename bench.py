@@ -71,7 +71,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -177,6 +177,7 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
     ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--clock-window-s", type=float, default=0.4, help="seconds of identical untimed steps run under the clock sampler right before the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
@@ -229,18 +230,31 @@ def main():
     for i in range(W):
         one_step(i)
     torch.cuda.synchronize(dev)
-    launches0 = sum(e.launch_count for e in envs)
-    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    # The timed region of a microsecond-scale step lasts milliseconds, shorter than nvidia-smi's sampling period, so the
+    # clock sampler runs over a window of identical untimed steps that leads straight into the K timed ones
+    # (continuous load, no idle gap); the window is named in the JSON.
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    t0 = time.perf_counter(); one_step(W); torch.cuda.synchronize(dev)
+    est = max(time.perf_counter() - t0, 2e-5)
+    if world > 1:                           # every rank must run the same number of steps (each carries a collective)
+        te = torch.tensor([est], dtype=torch.float64, device=dev)
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        est = float(te.item())
+    hold = int(min(20000, max(0, args.clock_window_s / est)))
+    for i in range(hold):
+        one_step(W + 1 + i)
+    W_eff = W + 1 + hold
+    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_start.record(stream)
+    launches0 = sum(e.launch_count for e in envs)
     for i in range(K):
-        one_step(W + i, pairs[i])
+        one_step(W_eff + i, pairs[i])
     if side is not None:
         stream.wait_stream(side)
     t_end.record(stream)
@@ -304,7 +318,7 @@ def main():
                          "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw) / D},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": E, "ms_per_step": e2e_ms / E, "api": "swarm_step_host (pinned host buffers, full obs D2H)"},
-            "gpu_launches": launches, "clocks": clocks,
+            "gpu_launches": launches, "clocks": dict(clocks, window=f"{hold} untimed steps + the {K} timed steps, continuous load"),
         }
         if world == 1 and not args.no_cpu_baseline:
             v, cores, sample, _ = cpu_port_throughput(kw, budget_s=12.0, scan_mode=0)

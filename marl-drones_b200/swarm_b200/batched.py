@@ -15,6 +15,7 @@ from ._lib import (ACT_I32, ACT_I64, ACT_U8, DTYPE_F32, DTYPE_U8, OBS_FULL, OBS_
                    STAT_NAMES, SwarmConfig, SwarmError, check)
 
 _ACT_DTYPES = {torch.uint8: ACT_U8, torch.int32: ACT_I32, torch.int64: ACT_I64}
+_raw_stream = torch._C._cuda_getCurrentRawStream   # (device_index) -> cudaStream_t as int; far cheaper than current_stream()
 
 
 class _DeviceView:
@@ -55,6 +56,13 @@ class BatchedDroneEnv:
         self._obs = torch.empty(self.obs_shape, dtype=obs_dtype, device=self.device)
         self._rew = torch.empty(n_envs, dtype=torch.float32, device=self.device)
         self._done = torch.empty(n_envs, dtype=torch.uint8, device=self.device)
+        # cached raw pointers / bound function for the per-step fast path (the tensors above live as long as self)
+        self._nact = n_envs * n_drones
+        self._dev_index = self.device.index
+        self._obs_ptr, self._rew_ptr, self._done_ptr = self._obs.data_ptr(), self._rew.data_ptr(), self._done.data_ptr()
+        self._stats_ptr = self.stats.data_ptr()
+        self._info = {"stats": self.stats}
+        self._step_fn = self._L.swarm_step
         ptr, nbytes = C.c_void_p(), C.c_int64()
         check(self._L.swarm_state_ptr(self._h, 0, C.byref(ptr), C.byref(nbytes)))
         #: resident positions float32 [N, D, 2] — a VIEW of the state (np.array(env.n_drones_pos), A2C/train.py:54,81)
@@ -88,21 +96,29 @@ class BatchedDroneEnv:
 
     def step(self, actions, out=None, want_obs=True):
         """A2C/envs.py:81-93. actions: integer tensor [N, D] on the device. Returns (obs, rewards, dones, infos);
-        infos holds the int64[8] running statistics tensor, still on the device."""
-        if not torch.is_tensor(actions):
-            actions = torch.as_tensor(np.asarray(actions), device=self.device)
-        if actions.dtype not in _ACT_DTYPES:
-            actions = actions.to(torch.int64)
-        actions = actions.to(self.device).contiguous()
-        if actions.numel() != self.num_envs * self.n_drones:
+        infos holds the int64[8] running statistics tensor, still on the device.
+        The common case (contiguous uint8/int32/int64 CUDA tensor) goes straight to the C ABI: one kernel launch."""
+        if not (torch.is_tensor(actions) and actions.dtype in _ACT_DTYPES and actions.device == self.device
+                and actions.is_contiguous()):
+            if not torch.is_tensor(actions):
+                actions = torch.as_tensor(np.asarray(actions), device=self.device)
+            if actions.dtype not in _ACT_DTYPES:
+                actions = actions.to(torch.int64)
+            actions = actions.to(self.device).contiguous()
+        if actions.numel() != self._nact:
             raise AssertionError("provide actions for each drone")      # A2C/noVis_sim.py:114
-        obs = None
+        obs, optr = None, None
         if want_obs:
-            obs = self._obs if out is None else out
-            self._chk_tensor(obs, self.obs_dtype, self._obs.numel(), "out")
-        check(self._L.swarm_step(self._h, self._ptr(actions), _ACT_DTYPES[actions.dtype], self._ptr(obs),
-                                 self._ptr(self._rew), self._ptr(self._done), self._ptr(self.stats), self._stream()))
-        return obs, self._rew, self._done, {"stats": self.stats}
+            if out is None:
+                obs, optr = self._obs, self._obs_ptr
+            else:
+                self._chk_tensor(out, self.obs_dtype, self._obs.numel(), "out")
+                obs, optr = out, out.data_ptr()
+        rc = self._step_fn(self._h, actions.data_ptr(), _ACT_DTYPES[actions.dtype], optr, self._rew_ptr, self._done_ptr,
+                           self._stats_ptr, _raw_stream(self._dev_index))
+        if rc:
+            check(rc)
+        return obs, self._rew, self._done, self._info
 
     def rollout(self, actions, obs_out=None, obs_last_only=False, reward_out=None, done_out=None):
         """T steps in one launch. actions uint8 [T, N, D]. Returns (obs_out, rewards [T, N], dones [T, N])."""
@@ -198,8 +214,5 @@ class BatchedDroneEnv:
 
     def allreduce_stats(self, group=None):
         """The only collective on this path: ncclAllReduce(SUM, int64[8]) of the episode statistics (64 B per rank)."""
-        import torch.distributed as dist
-        out = self.stats.clone()
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-            dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)
-        return out
+        from .sharding import reduce_stats
+        return reduce_stats(self.stats.clone(), group=group)

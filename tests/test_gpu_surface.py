@@ -178,3 +178,27 @@ def test_launcher_installs_facade_module():
     finally:
         if saved is not None:
             sys.modules["noVis_sim"] = saved
+
+
+def test_sharding_invariance_on_one_gpu():
+    """Two shards keyed by global env id (env_id_base) reproduce the unsharded batch env for env."""
+    import numpy as np
+    from swarm_b200 import BatchedDroneEnv, shard_range
+    kw = dict(row_count=16, col_count=16, n_drones=8, step_size=1.0, auto_reset=True, seed=123, obs_mode="window", window=5)
+    total, T = 301, 150
+    full = BatchedDroneEnv(total, **kw)
+    shards = []
+    for r in range(3):
+        first, count = shard_range(total, r, 3)
+        shards.append((first, count, BatchedDroneEnv(count, env_id_base=first, **kw)))
+    acts = torch.randint(0, 4, (T, total, 8), dtype=torch.uint8, device="cuda")
+    for t in range(T):
+        of, rf, df, _ = full.step(acts[t])
+        for first, count, e in shards:
+            o, r, d, _ = e.step(acts[t, first:first + count].contiguous())
+            assert torch.equal(o, of[first:first + count]) and torch.equal(r, rf[first:first + count])
+            assert torch.equal(d, df[first:first + count])
+    tot = sum(e.stats for _, _, e in shards)
+    assert torch.equal(tot, full.stats)
+    for first, count, e in shards:
+        assert torch.equal(e.pos, full.pos[first:first + count]) and torch.equal(e.meta, full.meta[first:first + count])
