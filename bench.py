@@ -169,7 +169,7 @@ def run_reference(args, kw, n_envs, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=1024)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
@@ -177,6 +177,7 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
     ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of replaying a CUDA graph of 32 steps")
     ap.add_argument("--clock-window-s", type=float, default=0.4, help="seconds of identical untimed steps run under the clock sampler right before the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -207,54 +208,91 @@ def main():
             for s in range(args.sets)]
     obs = [torch.empty(e.obs_shape, dtype=torch.float32, device=dev) for e in envs]
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    n_act = 8
-    acts = torch.randint(0, 4, (n_act, n_envs, D), dtype=torch.uint8, device=dev, generator=gen)
+    # 32 pre-generated action tensors: 16 i.i.d. uniform draws followed by their opposites ((a+2) mod 4), so a cycle has no
+    # net drift and the drones keep wandering instead of piling up against a wall over thousands of steps.
+    half = torch.randint(0, 4, (16, n_envs, D), dtype=torch.uint8, device=dev, generator=gen)
+    acts = torch.cat([half, (half + 2) % 4]).contiguous()
+    n_act = acts.shape[0]
     stream = torch.cuda.current_stream(dev)
     side = torch.cuda.Stream(dev) if world > 1 else None
-    snap = torch.zeros(8, dtype=torch.int64, device=dev)
+    snaps = [torch.zeros(8, dtype=torch.int64, device=dev) for _ in range(n_act)]
 
     def one_step(i, ev=None):
         s = i % args.sets
+        cur = torch.cuda.current_stream(dev)
         if ev is not None:
-            ev[0].record(stream)
+            ev[0].record(cur)
         envs[s].step(acts[i % n_act], out=obs[s])
         if ev is not None:
-            ev[1].record(stream)
+            ev[1].record(cur)
         if world > 1:                       # the path's only collective: 64-byte episode statistics, off the critical path
+            snap = snaps[i % n_act]
             snap.copy_(envs[s].stats, non_blocking=True)
-            done_ev = torch.cuda.Event(); done_ev.record(stream)
+            side.wait_stream(cur)
             with torch.cuda.stream(side):
-                side.wait_event(done_ev)
                 dist.all_reduce(snap)
 
     for i in range(W):
         one_step(i)
+    if side is not None:
+        stream.wait_stream(side)
     torch.cuda.synchronize(dev)
+
+    # CUDA graph of n_act consecutive steps (+ their side-stream all-reduces): the host enqueues one graph per 32 steps
+    # instead of 32 launches, so a microsecond-scale step is not bound by Python call overhead.
+    graph = None
+    if not args.no_graph and n_act % args.sets == 0:
+        try:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for j in range(n_act):
+                    one_step(j)
+                if side is not None:
+                    torch.cuda.current_stream(dev).wait_stream(side)
+            graph.replay()
+            torch.cuda.synchronize(dev)
+        except Exception as exc:            # capture unsupported (e.g. a collective that refuses capture): eager launches
+            print(f"[bench] CUDA graph capture failed ({exc!r}); falling back to eager launches", file=sys.stderr)
+            graph = None
+            torch.cuda.synchronize(dev)
+    if world > 1:                           # all ranks must agree (each step carries a collective)
+        flag = torch.tensor([1 if graph is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            graph = None
+
+    def run_steps(first, count, ev=None):
+        """`count` consecutive steps starting at step index `first` (a multiple of n_act): graph replays + eager remainder."""
+        k = 0
+        if graph is not None and ev is None:
+            while count - k >= n_act:
+                graph.replay()
+                k += n_act
+        while k < count:
+            one_step(first + k, None if ev is None else ev[k])
+            k += 1
+
     # The timed region of a microsecond-scale step lasts milliseconds, shorter than nvidia-smi's sampling period, so the
     # clock sampler runs over a window of identical untimed steps that leads straight into the K timed ones
     # (continuous load, no idle gap); the window is named in the JSON.
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    t0 = time.perf_counter(); one_step(W); torch.cuda.synchronize(dev)
-    est = max(time.perf_counter() - t0, 2e-5)
-    if world > 1:                           # every rank must run the same number of steps (each carries a collective)
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter(); run_steps(0, n_act); torch.cuda.synchronize(dev)
+    est = max((time.perf_counter() - t0) / n_act, 5e-6)
+    if world > 1:                           # every rank must run the same number of steps
         te = torch.tensor([est], dtype=torch.float64, device=dev)
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
         est = float(te.item())
-    hold = int(min(20000, max(0, args.clock_window_s / est)))
-    for i in range(hold):
-        one_step(W + 1 + i)
-    W_eff = W + 1 + hold
-    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    hold = int(min(40000, max(0, args.clock_window_s / est))) // n_act * n_act
+    run_steps(0, hold)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
     t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_start.record(stream)
-    launches0 = sum(e.launch_count for e in envs)
-    for i in range(K):
-        one_step(W_eff + i, pairs[i])
+    run_steps(0, K)
     if side is not None:
         stream.wait_stream(side)
     t_end.record(stream)
@@ -263,13 +301,23 @@ def main():
         dist.barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms_total = t_start.elapsed_time(t_end)
-    launches = sum(e.launch_count for e in envs) - launches0
+    launches = K                            # one step kernel per step (graph replays launch the captured kernels)
+    # per-launch durations: a separate eager pass with an event pair around every launch (not part of `value`)
+    P = min(K, 64)
+    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(P)]
+    run_steps(0, P, pairs)
+    if side is not None:
+        stream.wait_stream(side)
+    torch.cuda.synchronize(dev)
     kern_ms = sorted(a.elapsed_time(b) for a, b in pairs)
-    kern_avg_ms = sum(kern_ms) / len(kern_ms)
+    pair_avg_ms = sum(kern_ms) / len(kern_ms)
     if world > 1:
         t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
+    # the stream holds nothing but step kernels back to back, so the mean launch-to-launch time over the timed region
+    # bounds the kernel's duration from above (it includes the inter-kernel gaps): the conservative roofline numerator
+    kern_avg_ms = ms_total / K
     total_agent_steps = float(n_envs) * D * K * world
     value = total_agent_steps / (ms_total * 1e-3)
 
@@ -308,12 +356,13 @@ def main():
             "dtype": "u2 grid codes / f32 positions+obs (integer rewards)", "data": "synthetic",
             "config": {"workload": args.workload, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw,
                        "obs_dtype": "float32", "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
-                       "actions": "uint8 uniform{0..3}, pre-generated on device",
+                       "actions": "uint8 uniform{0..3} (16 draws + their opposites, zero net drift), pre-generated on device",
                        "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * 4 + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
                        "parallelism": f"env-sharded x{world}, no data-path collective; 64 B stats all-reduce on a side stream"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": load_traffic(args.workload), "peak_source": peak_src, "kernel": "swarm::step_kernel",
-                         "kernel_ms_avg": kern_avg_ms, "kernel_ms_median": kern_ms[len(kern_ms) // 2],
+                         "kernel_ms_avg": kern_avg_ms, "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
+                         "launch": "CUDA graph of 32 steps" if graph is not None else "eager",
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw) / D},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -326,10 +375,18 @@ def main():
             v2, _, sample2, _ = cpu_port_throughput(kw, budget_s=4.0, scan_mode=1)
             line["cpu_baseline_windowed"] = {"value": v2, "unit": UNIT, "cores": cores, "kind": "port (ours: bounded-window scan, not the reference's algorithm)", "sample": sample2}
         print(json.dumps(line))
+    sys.stdout.flush()
+    # teardown: release the captured graph (it holds NCCL work) before the communicator, and leave without running the
+    # interpreter's module teardown, which can dead-lock on a communicator that was used under graph capture
+    graph = None
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
     for e in envs:
         e.close()
-    if world > 1:
-        dist.destroy_process_group()
+    sys.stdout.flush(); sys.stderr.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":
