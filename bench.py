@@ -360,7 +360,7 @@ def main():
                        "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * 4 + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
                        "parallelism": f"env-sharded x{world}, no data-path collective; 64 B stats all-reduce on a side stream"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": load_traffic(args.workload), "peak_source": peak_src, "kernel": "swarm::step_kernel",
+                         "traffic": load_traffic(args.workload), "peak_source": peak_src, "kernel": "swarm::step_warp_kernel (swarm::step_cta_kernel for cfg5a/cfg5b)",
                          "kernel_ms_avg": kern_avg_ms, "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
                          "launch": "CUDA graph of 32 steps" if graph is not None else "eager",
                          "algorithmic_bytes_per_launch": bytes_per_launch,
