@@ -85,6 +85,29 @@ __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, u
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes)
                : "memory");
 }
+// variants taking 32-bit shared-memory addresses computed once (saves the generic->shared conversion per use)
+__device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar_s, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_s(uint32_t dst_s, const void* src_gmem, uint32_t bytes, uint32_t bar_s) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(src_gmem),
+               "r"(bytes), "r"(bar_s)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait_s(uint32_t bar_s, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "SWARM_WAITS_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra SWARM_DONES_%=;\n"
+      "bra SWARM_WAITS_%=;\n"
+      "SWARM_DONES_%=:\n"
+      "}\n" ::"r"(bar_s), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g_s(void* dst_gmem, uint32_t src_s, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(src_s), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 

@@ -174,7 +174,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   __shared__ uint64_t bars[8][2];
   __shared__ unsigned long long s_stats[6];
   __shared__ float4 lut4[(MODE == 1 && sizeof(OT) == 4) ? 256 : 1];   // byte of four codes -> four floats (WINDOW, float obs)
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const int wib = __shfl_sync(FULL, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform: group bookkeeping runs on the uniform datapath
   const int flags = FAST ? (F_ALL | (io.flags & F_RESET)) : io.flags;
   const bool cd_fast = FAST ? true : (p.cd_fast != 0);
   const bool has_wait = FAST ? false : (p.has_wait != 0);
@@ -208,19 +209,28 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   long long acc_rew = 0, acc_len = 0, acc_ret = 0;
   int acc_done = 0, acc_cells = 0, acc_anom = 0;
 
-  // lane 0: request the inputs of group `g` into buffer `b`
+  // lane 0: request the inputs of group `g` into buffer `b`.  Full groups take the four-copy path with constant sizes;
+  // the (single) partial tail group moves only its grid and meta by TMA and loads positions / actions directly.
+  const uint32_t in_s = smem_u32(inbuf0), bar_s = smem_u32(&bars[wib][0]), stage_s = smem_u32(stage);
+  const bool pos_tma_c = ((EPW * D * 8) & 15) == 0;
+  const bool act_tma_c = act_tma_ok && ((EPW * D) & 15) == 0 && io.T == 1;
+  const uint32_t gbytes_c = (uint32_t)EPW * (uint32_t)env_words * 4u, posb_c = (uint32_t)EPW * (uint32_t)D * 8u;
+  const uint32_t tx_c = gbytes_c + (pos_tma_c ? posb_c : 0u) + (meta_tma ? (uint32_t)EPW * 16u : 0u) + (act_tma_c ? (uint32_t)(EPW * D) : 0u);
   auto prefetch = [&](int g, int b) {
-    const int e0 = g * EPW, ne = min(EPW, N - e0);
-    unsigned char* in = inbuf0 + b * p.in_bytes;
-    uint64_t* bar = &bars[wib][b];
-    const uint32_t gbytes = (uint32_t)ne * (uint32_t)env_words * 4u, nd = (uint32_t)ne * (uint32_t)D;
-    const bool pos_tma = ((nd * 8u) & 15u) == 0 && (((uint32_t)e0 * (uint32_t)D * 8u) & 15u) == 0;
-    const bool act_tma = act_tma_ok && (nd & 15u) == 0 && (((uint32_t)e0 * (uint32_t)D) & 15u) == 0 && io.T == 1;
-    mbar_expect_tx(bar, gbytes + (pos_tma ? nd * 8u : 0u) + (meta_tma ? (uint32_t)ne * 16u : 0u) + (act_tma ? nd : 0u));
-    bulk_g2s(in, p.grid + (size_t)e0 * env_words, gbytes, bar);
-    if (pos_tma) bulk_g2s(in + p.off_pos, p.pos + (size_t)e0 * D, nd * 8u, bar);
-    if (meta_tma) bulk_g2s(in + p.off_meta, p.meta + e0, (uint32_t)ne * 16u, bar);
-    if (act_tma) bulk_g2s(in + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, nd, bar);
+    const int e0 = g * EPW;
+    const uint32_t dst = in_s + (uint32_t)b * (uint32_t)p.in_bytes, bs = bar_s + 8u * (uint32_t)b;
+    if (e0 + EPW <= N) {
+      mbar_expect_tx_s(bs, tx_c);
+      bulk_g2s_s(dst, p.grid + (size_t)e0 * env_words, gbytes_c, bs);
+      if (pos_tma_c) bulk_g2s_s(dst + p.off_pos, p.pos + (size_t)e0 * D, posb_c, bs);
+      if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, (uint32_t)EPW * 16u, bs);
+      if (act_tma_c) bulk_g2s_s(dst + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, (uint32_t)(EPW * D), bs);
+    } else {
+      const uint32_t ne = (uint32_t)(N - e0);
+      mbar_expect_tx_s(bs, ne * (uint32_t)env_words * 4u + (meta_tma ? ne * 16u : 0u));
+      bulk_g2s_s(dst, p.grid + (size_t)e0 * env_words, ne * (uint32_t)env_words * 4u, bs);
+      if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, ne * 16u, bs);
+    }
   };
 
   uint32_t phases = 0;
@@ -236,9 +246,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     const bool active = valid && tl < D;
     uint32_t* const sg = sgrid + tile * env_words;
     uint32_t* const gg = p.grid + (size_t)env * env_words;
-    const uint32_t nd = (uint32_t)nenv * (uint32_t)D;
-    const bool pos_tma = ((nd * 8u) & 15u) == 0 && (((uint32_t)env0 * (uint32_t)D * 8u) & 15u) == 0;
-    const bool act_tma = act_tma_ok && (nd & 15u) == 0 && (((uint32_t)env0 * (uint32_t)D) & 15u) == 0 && io.T == 1;
+    const bool full = nenv == EPW;
+    const bool pos_tma = pos_tma_c && full, act_tma = act_tma_c && full;
     float2* const pp = p.pos + (size_t)env * D + (active ? tl : 0);
     size_t aidx = (size_t)env * D + tl;                 // action index, advanced by N*D per step
     size_t ridx = (size_t)env;                          // reward / done index, advanced by N per step
@@ -250,7 +259,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     if (active && !pos_tma) q = __ldcg(pp);
     if (active && !act_tma && (flags & F_MOVE)) a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
 
-    mbar_wait(&bars[wib][b], (phases >> b) & 1u);
+    mbar_wait_s(bar_s + 8u * (uint32_t)b, (phases >> b) & 1u);
     phases ^= 1u << b;
     // the other buffer's readers finished before the fence that ended the previous group: refill it now
     if (lane == 0 && grp + nw < ngroups) prefetch(grp + nw, b ^ 1);
@@ -390,7 +399,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
           const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(OT);
           if ((((uintptr_t)dst) & 15) == 0 && (bytes & 15u) == 0) {
             if (lane == 0) {   // one TMA bulk store for the whole group
-              bulk_s2g(dst, stage, bytes);
+              bulk_s2g_s(dst, stage_s, bytes);
               bulk_commit();
             }
           } else {
