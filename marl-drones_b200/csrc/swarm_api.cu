@@ -68,7 +68,6 @@ extern "C" int swarm_device_count(void) {
 
 // ---- kernel selection ------------------------------------------------------------------------------------------------
 constexpr int kWarpSmemMax = 20 * 1024;     // per-warp shared-memory slice the staged kernel may use
-constexpr int kCtaSmemMax = 200 * 1024;
 
 static int stage_bytes_for(const SwarmConfig* c, int epw) {
   if (c->obs_mode != SWARM_OBS_WINDOW) return 16;
@@ -311,10 +310,19 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st
       default: err = launch_warp_ts<32, OT>(e, io, st, blocks, smem); break;
     }
   } else {
+    // one CTA per env; the env's packed grid is staged in shared memory when it fits (160 KB = 640k cells)
+    const long long need = (long long)p.env_words * 4 + 16;
+    const int staged = need <= 160 * 1024;
+    const int smem = staged ? (int)need : 0;
+    if (!e->resident[0]) {
+      if (staged && (err = cudaFuncSetAttribute(step_cta_kernel<OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return err;
+      int per_sm = 0;
+      if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_cta_kernel<OT>, 256, smem)) != cudaSuccess) return err;
+      e->resident[0] = (per_sm > 0 ? per_sm : 1) * e->sm_count;
+    }
     long long blocks = p.N;
-    const long long cap = (long long)e->sm_count * 8;       // 8 resident CTAs of 256 threads per SM, grid-stride beyond
-    if (blocks > cap) blocks = cap;
-    step_cta_kernel<OT><<<(int)blocks, 256, 0, st>>>(p, io);
+    if (blocks > e->resident[0]) blocks = e->resident[0];   // resident CTAs only, grid-stride beyond
+    step_cta_kernel<OT><<<(int)blocks, 256, smem, st>>>(p, io, staged);
   }
   e->launches++;
   return err;

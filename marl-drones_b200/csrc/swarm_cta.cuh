@@ -1,7 +1,9 @@
 // swarm_cta.cuh — the fused env step for shapes the shared-memory-staged kernel does not take: more than 32 drones per
 // env, or a packed grid too large to stage per warp (the 256x256 stress config).  One CTA per env:
-//   warp 0 runs stages (1)-(3) on the HBM-resident grid in index-ordered chunks of 32 drones,
-//   then the WHOLE CTA streams stage (4) (a 256x256 full obs is 256 KiB per env: the emission is the kernel).
+//   one TMA bulk copy brings the env's packed grid (16 KiB at 256x256) into the CTA's shared memory,
+//   warp 0 runs stages (1)-(3) in index-ordered chunks of 32 drones (clears go to shared memory and, write-through, to HBM),
+//   then the WHOLE CTA streams stage (4) from shared memory with 128-bit stores (a 256x256 float obs is 256 KiB per env:
+//   the emission is the kernel).  Grids beyond the shared-memory budget fall back to the HBM-resident grid.
 // Reference lines per stage: see swarm_step.cuh.
 #pragma once
 #include "swarm_common.cuh"
@@ -11,7 +13,8 @@
 namespace swarm {
 
 // Stages (1)-(3) (+ auto-reset) of one env by one warp.
-__device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc) {
+// `sg`: the env's packed grid in shared memory (null = work on the HBM copy only).
+__device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc, uint32_t* sg) {
   constexpr int TS = 32;
   const int flags = io.flags;
   const int D = p.D;
@@ -55,7 +58,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
         const int k = __popc(m);
         uint32_t* wp = g + (cell >> 4);
         const int sh = (cell & 15) * 2;
-        const uint32_t code = (ld_grid(wp) >> sh) & 3u;
+        const uint32_t code = ((sg ? sg[cell >> 4] : ld_grid(wp)) >> sh) & 3u;
         if (code) {
           bool clear = true;
           if (p.has_wait) {   // dwell (App. B.2)
@@ -66,6 +69,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
           }
           if (clear) {
             atomicAnd(wp, ~(3u << sh));
+            if (sg) atomicAnd(sg + (cell >> 4), ~(3u << sh));
             rew += 10 + (code == 2u ? 20 : 0);   // 10 + _check_uncertain_mapped (noVis_sim.py:83-84,104-110)
             ncl += 1;
             nan += (code == 2u);
@@ -77,7 +81,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
   }
   if ((flags & F_SCATTER) && !p.cd_fast) {
     __syncwarp();
-    if (lane == 0) scatter_sequential(p, env, g, nullptr, rew, ncl, nan);
+    if (lane == 0) scatter_sequential(p, env, g, sg, rew, ncl, nan);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -113,7 +117,11 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
     }
     do_reset = __shfl_sync(FULL, (int)do_reset, 0) != 0;
     const int episode = __shfl_sync(FULL, m.w, 0);
-    if (do_reset) reset_tile<TS>(p, env, episode + 1, lane, true);
+    if (do_reset) {
+      reset_tile<TS>(p, env, episode + 1, lane, true);
+      if (sg)   // refresh the shared-memory copy from the freshly written HBM grid
+        for (int w = lane; w < p.env_words; w += 32) sg[w] = ld_grid(g + w);
+    }
   } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
     if (lane == 0) {
       io.cover_out[env] = rew;
@@ -123,25 +131,86 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
   __syncwarp();
 }
 
+// CTA-wide stage (4) from the shared-memory grid.
 template <typename OT>
-__global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
+__device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint32_t* sg, int env, int tid, int nthr, OT* __restrict__ obs) {
+  const ObsCvt<OT> cvt(p);
+  if (p.obs_mode == 0) {
+    const int RC = p.RC;
+    OT* o = obs + (size_t)env * RC;
+    if ((RC & 3) == 0 && ((uintptr_t)o & 15) == 0) {
+      const int nq = RC >> 2;
+#pragma unroll 4
+      for (int q = tid; q < nq; q += nthr) cvt.store4(o + 4 * q, (sg[q >> 2] >> ((q & 3) * 8)) & 0xffu);
+    } else {
+      for (int c = tid; c < RC; c += nthr) o[c] = cvt.one((sg[c >> 4] >> ((c & 15) * 2)) & 3u);
+    }
+  } else {   // one item = one window row of one drone
+    const int W = p.W, WW = W * W, h = (W - 1) >> 1, nitem = p.D * W;
+    const float2* ps = p.pos + (size_t)env * p.D;
+    OT* o = obs + (size_t)env * p.D * WW;
+    for (int it = tid; it < nitem; it += nthr) {
+      const int i = it / W, b = it - i * W;
+      const float2 q = __ldcg(ps + i);
+      const int cx = (int)floorf(q.x + 0.5f), gy = (int)floorf(q.y + 0.5f) - h + b;
+      OT* dst = o + (size_t)i * WW + b * W;
+      const bool row_ok = (unsigned)gy < (unsigned)p.C;
+      for (int a = 0; a < W; ++a) {
+        const int gx = cx - h + a;
+        uint32_t code = 3u;
+        if (row_ok && (unsigned)gx < (unsigned)p.R) {
+          const int cell = gy * p.R + gx;
+          code = (sg[cell >> 4] >> ((cell & 15) * 2)) & 3u;
+        }
+        dst[a] = cvt.one(code);
+      }
+    }
+  }
+}
+
+// `staged` != 0: dynamic shared memory holds env_words words (+ slack) and the grid is staged through it.
+template <typename OT>
+__global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io, int staged) {
+  extern __shared__ __align__(128) unsigned char cta_smem[];
+  __shared__ uint64_t bar;
+  uint32_t* const sg = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int flags = io.flags;
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
   const bool stepping = (flags & (F_MOVE | F_SCATTER | F_REWARD)) != 0;
+  if (staged && threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  uint32_t phase = 0;
   StatAcc acc;
-  for (int env = blockIdx.x; env < p.N; env += gridDim.x)
+  for (int env = blockIdx.x; env < p.N; env += gridDim.x) {
+    if (staged) {
+      if (threadIdx.x == 0) {   // one TMA bulk copy: the env's whole packed grid
+        mbar_expect_tx(&bar, (uint32_t)p.env_words * 4u);
+        bulk_g2s(sg, p.grid + (size_t)env * p.env_words, (uint32_t)p.env_words * 4u, &bar);
+      }
+      mbar_wait(&bar, phase);
+      phase ^= 1u;
+    }
     for (int t = 0; t < io.T; ++t) {
       if (stepping) {
-        if (warp == 0) step_env_warp(p, io, t, env, lane, acc);
-        __syncthreads();   // warp 0's grid / position updates (L2) are visible to the CTA
+        if (warp == 0) step_env_warp(p, io, t, env, lane, acc, sg);
+        __syncthreads();   // warp 0's grid / position updates are visible to the CTA
       }
       if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
         OT* o = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * p.N * p.obs_per_env);
-        emit_obs_global<OT>(p, env, threadIdx.x, blockDim.x, o);
+        if (staged) emit_obs_cta_smem<OT>(p, sg, env, threadIdx.x, blockDim.x, o);
+        else emit_obs_global<OT>(p, env, threadIdx.x, blockDim.x, o);
         if (stepping && t + 1 < io.T) __syncthreads();   // emission reads precede the next step's clears
       }
     }
+    if (staged) {
+      fence_proxy_async();   // generic accesses to the staged grid precede the next env's bulk copy
+      __syncthreads();
+    }
+  }
 
   if (io.stats && (flags & F_REWARD)) {   // only warp 0 accumulated
     if (warp == 0) {
