@@ -94,10 +94,6 @@ static int pick_tile(const SwarmConfig* c, int sms, DevParams* p) {
     const long long ws = (long long)stage + 2 * in_bytes + 16;
     if (ws <= kWarpSmemMax) {
       p->stage_bytes = stage;
-      p->in_bytes = (int)in_bytes;
-      p->off_pos = gridb;
-      p->off_meta = gridb + posb;
-      p->off_act = gridb + posb + metab;
       p->warp_smem = (int)ws;
       return ts;
     }
@@ -187,6 +183,16 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
       long long warps = ctas * w;
       if (warps > 32) warps = 32;
       if (warps > best) { best = (int)warps; e->wpb = w; }
+    }
+    if (e->staged) {   // CTA-level input buffer for EPC = wpb * EPW envs
+      const long long epc = (long long)e->wpb * (32 / e->ts);
+      const int gridb = (int)(epc * p.env_words * 4), posb = align16(epc * c->n_drones * 8), metab = (int)(epc * 16);
+      const int actb = align16(epc * c->n_drones);
+      p.off_pos = gridb;
+      p.off_meta = gridb + posb;
+      p.off_act = gridb + posb + metab;
+      p.in_bytes = gridb + posb + metab + actb;
+      p.cta_smem = e->wpb * p.stage_bytes + 2 * p.in_bytes + 16;
     }
   }
   p.nq_magic = RC >= 4 ? (uint32_t)(((1ull << 32) + (uint64_t)(RC / 4) - 1) / (uint64_t)(RC / 4)) : 0u;
@@ -302,7 +308,7 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st
     const int epw = 32 / e->ts;
     const long long ngroups = ((long long)p.N + epw - 1) / epw;
     const long long blocks = (ngroups + e->wpb - 1) / e->wpb;
-    const int smem = e->wpb * p.warp_smem;
+    const int smem = p.cta_smem;
     switch (e->ts) {
       case 4: err = launch_warp_ts<4, OT>(e, io, st, blocks, smem); break;
       case 8: err = launch_warp_ts<8, OT>(e, io, st, blocks, smem); break;

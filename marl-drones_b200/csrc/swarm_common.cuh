@@ -35,9 +35,11 @@ struct DevParams {
   double spread2_thr; // largest double z with sqrt(z) <= spread_thr: sqrt(d2) > thr <=> d2 > spread2_thr
   // warp-autonomous staged kernel (swarm_warp.cuh): per-warp shared-memory carve-up, bytes
   int stage_bytes;    // obs staging (WINDOW mode), multiple of 16, >= 16
-  int in_bytes;       // one input buffer: [grid EPW*env_words*4][pos EPW*D*8][meta EPW*16][actions EPW*D], each 16 B aligned
+  int in_bytes;       // one CTA input buffer for EPC = wpb*EPW envs: [grid EPC*env_words*4][pos EPC*D*8][meta EPC*16][actions EPC*D],
+                      // each part 16 B aligned
   int off_pos, off_meta, off_act;   // byte offsets inside an input buffer
-  int warp_smem;      // stage_bytes + 2 * in_bytes + 16
+  int warp_smem;      // per-warp footprint used to size the CTA (stage_bytes + 2 * per-warp inputs + slack)
+  int cta_smem;       // dynamic shared memory of a CTA: wpb * stage_bytes + 2 * in_bytes + 16
   uint32_t nq_magic;  // ceil(2^32 / (RC/4)) for the FULL-mode vector -> (env, quad) split
   uint32_t seed_lo, seed_hi;
   long long env_id_base;
@@ -104,6 +106,9 @@ __device__ __forceinline__ void mbar_wait_s(uint32_t bar_s, uint32_t parity) {
       "bra SWARM_WAITS_%=;\n"
       "SWARM_DONES_%=:\n"
       "}\n" ::"r"(bar_s), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_s(uint32_t bar_s) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_s) : "memory");
 }
 __device__ __forceinline__ void bulk_s2g_s(void* dst_gmem, uint32_t src_s, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(src_s), "r"(bytes) : "memory");

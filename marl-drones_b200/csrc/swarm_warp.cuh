@@ -171,7 +171,7 @@ template <int TS, typename OT, int MODE, int WC, bool FAST>
 __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
   constexpr int EPW = 32 / TS;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ uint64_t bars[8][2];
+  __shared__ uint64_t full_bar[2], empty_bar[2];   // per input buffer: "inputs landed" (TMA tx count) / "all warps done with it"
   __shared__ unsigned long long s_stats[6];
   __shared__ float4 lut4[(MODE == 1 && sizeof(OT) == 4) ? 256 : 1];   // byte of four codes -> four floats (WINDOW, float obs)
   const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
@@ -185,20 +185,22 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   if constexpr (MODE == 1 && sizeof(OT) == 4) {
     for (int b = threadIdx.x; b < 256; b += blockDim.x) lut4[b] = make_float4(cvt.sel(b, 0), cvt.sel(b, 1), cvt.sel(b, 2), cvt.sel(b, 3));
   }
-  __syncthreads();
-  unsigned char* const wbase = smem_raw + (size_t)wib * p.warp_smem;
-  OT* const stage = reinterpret_cast<OT*>(wbase);                 // [EPW][D][W*W] obs staging (WINDOW)
-  unsigned char* const inbuf0 = wbase + p.stage_bytes;            // two input buffers of p.in_bytes each
-  if (lane == 0) {
-    mbar_init(&bars[wib][0], 1);
-    mbar_init(&bars[wib][1], 1);
+  if (threadIdx.x == 0) {
+    mbar_init(&full_bar[0], 1);
+    mbar_init(&full_bar[1], 1);
+    mbar_init(&empty_bar[0], (uint32_t)wpb);
+    mbar_init(&empty_bar[1], (uint32_t)wpb);
     fence_mbar_init();
   }
-  __syncwarp();
+  __syncthreads();
+  // CTA shared memory: [obs staging: wpb x stage_bytes][input buffer 0][input buffer 1][slack]
+  OT* const stage = reinterpret_cast<OT*>(smem_raw + (size_t)wib * p.stage_bytes);   // this warp's [EPW][D][W*W] staging (WINDOW)
+  unsigned char* const inbuf0 = smem_raw + (size_t)wpb * p.stage_bytes;              // two CTA input buffers of p.in_bytes each
   const int tile = lane / TS, tl = lane % TS, lead = tile * TS;
   const int D = p.D, N = p.N, env_words = p.env_words;
   const int ngroups = (N + EPW - 1) / EPW;
-  const int gw = blockIdx.x * wpb + wib, nw = gridDim.x * wpb;
+  const int EPC = wpb * EPW;                      // envs per CTA-iteration (wpb consecutive groups)
+  const int ncg = (N + EPC - 1) / EPC;            // CTA-groups
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
   const int WW = MODE == 1 ? (WC ? WC : p.W) * (WC ? WC : p.W) : 1;
   OT* const my_stage = stage + (tile * D + tl) * WW;
@@ -209,22 +211,23 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   long long acc_rew = 0, acc_len = 0, acc_ret = 0;
   int acc_done = 0, acc_cells = 0, acc_anom = 0;
 
-  // lane 0: request the inputs of group `g` into buffer `b`.  Full groups take the four-copy path with constant sizes;
-  // the (single) partial tail group moves only its grid and meta by TMA and loads positions / actions directly.
-  const uint32_t in_s = smem_u32(inbuf0), bar_s = smem_u32(&bars[wib][0]), stage_s = smem_u32(stage);
-  const bool pos_tma_c = ((EPW * D * 8) & 15) == 0;
-  const bool act_tma_c = act_tma_ok && ((EPW * D) & 15) == 0 && io.T == 1;
-  const uint32_t gbytes_c = (uint32_t)EPW * (uint32_t)env_words * 4u, posb_c = (uint32_t)EPW * (uint32_t)D * 8u;
-  const uint32_t tx_c = gbytes_c + (pos_tma_c ? posb_c : 0u) + (meta_tma ? (uint32_t)EPW * 16u : 0u) + (act_tma_c ? (uint32_t)(EPW * D) : 0u);
-  auto prefetch = [&](int g, int b) {
-    const int e0 = g * EPW;
-    const uint32_t dst = in_s + (uint32_t)b * (uint32_t)p.in_bytes, bs = bar_s + 8u * (uint32_t)b;
-    if (e0 + EPW <= N) {
+  // Producer (thread 0 of the CTA): request the inputs of CTA-group `cg` — wpb consecutive groups, contiguous in every
+  // array — into input buffer `b`: four bulk copies on full_bar[b].  The partial tail CTA-group moves only its grid and
+  // meta by TMA (their sizes are always multiples of 16 B) and its warps load positions / actions directly.
+  const uint32_t in_s = smem_u32(inbuf0), full_s = smem_u32(&full_bar[0]), empty_s = smem_u32(&empty_bar[0]), stage_s = smem_u32(stage);
+  const bool pos_tma_c = ((EPC * D * 8) & 15) == 0;
+  const bool act_tma_c = act_tma_ok && ((EPC * D) & 15) == 0 && io.T == 1;
+  const uint32_t gbytes_c = (uint32_t)EPC * (uint32_t)env_words * 4u, posb_c = (uint32_t)EPC * (uint32_t)D * 8u;
+  const uint32_t tx_c = gbytes_c + (pos_tma_c ? posb_c : 0u) + (meta_tma ? (uint32_t)EPC * 16u : 0u) + (act_tma_c ? (uint32_t)(EPC * D) : 0u);
+  auto produce = [&](int cg, int b) {
+    const int e0 = cg * EPC;
+    const uint32_t dst = in_s + (uint32_t)b * (uint32_t)p.in_bytes, bs = full_s + 8u * (uint32_t)b;
+    if (e0 + EPC <= N) {
       mbar_expect_tx_s(bs, tx_c);
       bulk_g2s_s(dst, p.grid + (size_t)e0 * env_words, gbytes_c, bs);
       if (pos_tma_c) bulk_g2s_s(dst + p.off_pos, p.pos + (size_t)e0 * D, posb_c, bs);
-      if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, (uint32_t)EPW * 16u, bs);
-      if (act_tma_c) bulk_g2s_s(dst + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, (uint32_t)(EPW * D), bs);
+      if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, (uint32_t)EPC * 16u, bs);
+      if (act_tma_c) bulk_g2s_s(dst + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, (uint32_t)(EPC * D), bs);
     } else {
       const uint32_t ne = (uint32_t)(N - e0);
       mbar_expect_tx_s(bs, ne * (uint32_t)env_words * 4u + (meta_tma ? ne * 16u : 0u));
@@ -234,20 +237,29 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   };
 
   uint32_t phases = 0;
-  if (gw < ngroups && lane == 0) prefetch(gw, 0);
+  const bool producer = threadIdx.x == 0;
+  if (producer && (int)blockIdx.x < ncg) produce(blockIdx.x, 0);
   int it = 0;
-  for (int grp = gw; grp < ngroups; grp += nw, ++it) {
+  for (int cg = blockIdx.x; cg < ncg; cg += gridDim.x, ++it) {
     const int b = it & 1;
+    // refill the other buffer for the CTA's next iteration as soon as every warp has released it (it was read in iteration
+    // it-1; its (it-1)/2-th release completes phase ((it-1)/2) & 1 of empty_bar[b^1])
+    if (producer && cg + (int)gridDim.x < ncg) {
+      if (it >= 1) mbar_wait_s(empty_s + 8u * (uint32_t)(b ^ 1), (uint32_t)((it - 1) >> 1) & 1u);
+      produce(cg + gridDim.x, b ^ 1);
+    }
+    const int grp = cg * wpb + wib;
+    if (grp >= ngroups) continue;   // idle warp of the tail CTA-group (last iteration only)
     unsigned char* const in = inbuf0 + b * p.in_bytes;
-    uint32_t* const sgrid = reinterpret_cast<uint32_t*>(in);
+    uint32_t* const sgrid = reinterpret_cast<uint32_t*>(in) + wib * EPW * env_words;
+    const bool cta_full = cg * EPC + EPC <= N;
     const int env0 = grp * EPW, nenv = min(EPW, N - env0);
     const bool valid = tile < nenv;
     const int env = valid ? env0 + tile : env0;
     const bool active = valid && tl < D;
     uint32_t* const sg = sgrid + tile * env_words;
     uint32_t* const gg = p.grid + (size_t)env * env_words;
-    const bool full = nenv == EPW;
-    const bool pos_tma = pos_tma_c && full, act_tma = act_tma_c && full;
+    const bool pos_tma = pos_tma_c && cta_full, act_tma = act_tma_c && cta_full;
     float2* const pp = p.pos + (size_t)env * D + (active ? tl : 0);
     size_t aidx = (size_t)env * D + tl;                 // action index, advanced by N*D per step
     size_t ridx = (size_t)env;                          // reward / done index, advanced by N per step
@@ -259,13 +271,11 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     if (active && !pos_tma) q = __ldcg(pp);
     if (active && !act_tma && (flags & F_MOVE)) a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
 
-    mbar_wait_s(bar_s + 8u * (uint32_t)b, (phases >> b) & 1u);
+    mbar_wait_s(full_s + 8u * (uint32_t)b, (phases >> b) & 1u);
     phases ^= 1u << b;
-    // the other buffer's readers finished before the fence that ended the previous group: refill it now
-    if (lane == 0 && grp + nw < ngroups) prefetch(grp + nw, b ^ 1);
-    if (active && pos_tma) q = reinterpret_cast<const float2*>(in + p.off_pos)[tile * D + tl];
-    if (active && act_tma) a = (int)in[p.off_act + tile * D + tl];
-    if (valid && tl == 0 && meta_tma) m = reinterpret_cast<const int4*>(in + p.off_meta)[tile];
+    if (active && pos_tma) q = reinterpret_cast<const float2*>(in + p.off_pos)[(wib * EPW + tile) * D + tl];
+    if (active && act_tma) a = (int)in[p.off_act + (wib * EPW + tile) * D + tl];
+    if (valid && tl == 0 && meta_tma) m = reinterpret_cast<const int4*>(in + p.off_meta)[wib * EPW + tile];
 
     for (int t = 0; t < io.T; ++t, aidx += (size_t)N * D, ridx += N) {
       if (t > 0 && active && (flags & F_MOVE))   // rollout: positions / meta are carried in registers, actions are re-read
@@ -409,8 +419,9 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
       }
       __syncwarp();
     }
-    fence_proxy_async();   // this group's generic accesses to its input buffer precede the bulk copy that refills it
+    fence_proxy_async();   // this group's generic accesses to the input buffer precede the bulk copy that refills it
     __syncwarp();
+    if (lane == 0) mbar_arrive_s(empty_s + 8u * (uint32_t)b);   // release the buffer to the producer
   }
   if (lane == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
 
