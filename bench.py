@@ -31,6 +31,7 @@ WORKLOADS = {
     "cfg5a": (1024, dict(row_count=256, col_count=256, n_drones=64, step_size=1.0, obs_mode="full")),
     "cfg5b": (1024, dict(row_count=256, col_count=256, n_drones=64, step_size=1.0, obs_mode="window", window=5)),
 }
+A2C_WORKLOAD = "cfg4_a2c"   # BASELINE configs[3]: the A2C/train.py rollout loop on the cfg4 env shape, env + policy end to end
 METRIC = "agent-steps/sec (device-timed)"
 UNIT = "agent-steps/s"
 
@@ -166,13 +167,131 @@ def run_reference(args, kw, n_envs, rank, world):
     }))
 
 
+def run_a2c(args, rank, world, local):
+    """BASELINE configs[3] / SURVEY §8f-1: the batched re-expression of A2C/train.py::train() — per outer iteration T =
+    --rollout-steps times (16 stacked MlpPolicy nets forward with autograd -> swarm_sample_actions -> fused env step), then the
+    bootstrap pass, swarm_nstep_returns, loss, backward, per-drone clip and AdamW.  A bench "step" is ONE outer iteration;
+    value = agent-steps/s = N * D * T * iterations / time, env + policy + update end to end, device-timed."""
+    n_envs, kw = WORKLOADS["cfg4"]
+    kw = dict(kw)
+    if args.envs:
+        n_envs = args.envs
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "metric": "agent-steps/sec (env+policy, A2C train loop)", "config": {"workload": A2C_WORKLOAD},
+                              "unavailable": "the reference train() is pure Python/PyTorch under /root/reference and cannot travel to the GPU box; "
+                                             "measured in the build container: 47.2 agent-steps/s (8 cores, 10x10, 8 drones, MLP; BASELINE.md)"}))
+        return
+    import torch
+    import torch.distributed as dist
+    from swarm_b200 import BatchedDroneEnv
+    from swarm_b200.a2c import A2CTrainer
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl ours) needs a B200; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cuda.matmul.allow_tf32 = bool(args.tf32)
+    D, T = kw["n_drones"], args.rollout_steps
+    K = args.steps if args.steps != 1024 else 10
+    W = max(args.warmup if args.warmup != 10 else 3, 3)
+    env = BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=rank * n_envs, **kw)
+    torch.manual_seed(1234)                                  # identical initial weights on every rank
+    tr = A2CTrainer(env, rollout_steps=T, seed=99 + rank)
+    for _ in range(W):
+        tr.train_iteration()
+    torch.cuda.synchronize(dev)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = env.launch_count
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(K):
+        tr.train_iteration()
+    t1.record()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = t0.elapsed_time(t1)
+    env_launches = env.launch_count - l0
+    # e2e: the same loop, reading the loss back to the host every iteration (the step's result); inputs are produced on the
+    # device by the env itself, so there is no per-step H2D
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    for _ in range(K):
+        float(tr.train_iteration().item())
+    torch.cuda.synchronize(dev)
+    e2e_ms = (time.perf_counter() - w0) * 1e3
+    # rollout only (no autograd, no update): the acting loop of a trained policy
+    with torch.no_grad():
+        tr.rollout(grad=False)
+        torch.cuda.synchronize(dev)
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record()
+        for _ in range(K):
+            tr.rollout(grad=False)
+        r1.record()
+        torch.cuda.synchronize(dev)
+    roll_ms = r0.elapsed_time(r1)
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms, roll_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms, roll_ms = (float(x) for x in t.tolist())
+    if rank == 0:
+        H = kw["row_count"] * kw["col_count"]
+        macs = 3 * H * H + H * H + H * 256 + 256 * 128 + 128 * 128 + 128 * 64 + 64 * 32 + 32 * 32   # one MlpPolicy, dense4 aside
+        flops_iter = 2.0 * macs * 2 * D * n_envs * (3 * T + 1)        # forward + backward (2x) over T steps, + the bootstrap forward
+        agent_steps = float(n_envs) * D * T * K * world
+        try:
+            peak = float(json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]); src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+        except Exception:
+            peak, src = 1500.0, "fallback (B200_PROFILING.md)"
+        ach = flops_iter * K / (ms * 1e-3) / 1e12
+        line = {
+            "metric": "agent-steps/sec (env+policy, A2C train loop, device-timed)", "value": agent_steps / (ms * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "tf32 policy GEMMs" if args.tf32 else "f32 (policy GEMMs via cuBLAS, as the reference's float32)", "data": "synthetic",
+            "config": {"workload": A2C_WORKLOAD, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw, "rollout_steps": T,
+                       "policy": "MLP (A2C/models.py MlpPolicy, actor+critic per drone = 16 nets, random init)", "optimizer": "AdamW lr 2e-4, per-drone clip 10",
+                       "step": "one outer iteration of train(): T x (policy fwd + sample + env step) + bootstrap + returns + loss + backward + update",
+                       "l2": "activations kept for backward: ~1 GB per rollout step, far beyond the 126 MB L2",
+                       "parallelism": f"data-parallel x{world}: envs sharded, one gradient all-reduce per iteration" if world > 1 else "single GPU"},
+            "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None, "peak_source": src,
+                         "kernel": "cuBLAS batched SGEMM behind torch.bmm (library GEMMs: this row is a caller of the hot path, not the hot path)",
+                         "algorithmic_flops_per_iteration": flops_iter},
+            "e2e": {"value": agent_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4, "steps": K,
+                    "ms_per_step": e2e_ms / K, "api": "A2CTrainer.train_iteration() + loss.item()"},
+            "rollout_only": {"value": agent_steps / (roll_ms * 1e-3), "unit": UNIT, "ms_per_step": roll_ms / K, "what": "no autograd, no update: policy fwd + sample + env step"},
+            "gpu_launches": int(env_launches + K * (T + 1)), "gpu_launches_note": "swarm_step + swarm_sample_actions per rollout step, swarm_nstep_returns + reset per iteration (torch/cuBLAS kernels not counted)",
+            "clocks": clocks,
+            "cpu_baseline": {"value": 47.2, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified A2C/train.py::train(), 250 env-steps, 10x10, 8 drones, MLP, measured in the build container (cannot travel to the GPU box)"},
+        }
+        print(json.dumps(line))
+    sys.stdout.flush()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    env.close()
+    sys.stdout.flush(); sys.stderr.flush()
+    os._exit(0)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=1024)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + [A2C_WORKLOAD])
+    ap.add_argument("--rollout-steps", type=int, default=25, help="cfg4_a2c: env steps per outer iteration (A2C/main.py default)")
+    ap.add_argument("--tf32", action="store_true", help="cfg4_a2c: allow TF32 tensor-core GEMMs for the policy (default: fp32, as the reference)")
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
@@ -183,6 +302,8 @@ def main():
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.workload == A2C_WORKLOAD:
+        return run_a2c(args, rank, world, local)
     n_envs, kw = WORKLOADS[args.workload]
     kw = dict(kw)
     if args.envs:

@@ -173,6 +173,21 @@ int swarm_stage_obs(SwarmEnv* env, void* obs_out, void* stream);
 /* Greedy nearest-unmapped-cell pursuit restricted to the 4 noVis actions; writes uint8[N][D]. */
 int swarm_greedy_actions(SwarmEnv* env, uint8_t* actions_out, void* stream);
 
+/* -- batched A2C rollout helpers (stateless, buffers on the current device) ---- */
+/* softmax + Categorical(probs).sample() of A2C/train.py:66-73 for every (env, drone):
+ * logits float32 [D][N][A] (16 B aligned when A == 4) -> actions uint8 [N][D], the env's action layout.
+ * u ~ Philox4x32-10 keyed by (seed; env_id_base + n, step, d / 4); a = #{k : cum_k <= u * sum}. */
+int swarm_sample_actions(const float* logits, int32_t n_drones, int64_t n_envs, int32_t n_actions,
+                         uint64_t seed, uint32_t step, int64_t env_id_base, uint8_t* actions_out,
+                         void* stream);
+/* process_rollout's reverse scan (A2C/train.py:160-183): returns[t] = rewards[t] + returns[t+1] * gamma * (1 - dones[t])
+ * in float32 with the reference's operation order, bootstrapped from last_values.
+ * rewards float32 [T][N], dones uint8 [T][N], last_values float32 [D][N] -> returns float32 [T][D][N];
+ * coef_out (may be NULL) float32 [T][N] = prod_{s>=t} gamma * (1 - dones[s]) = d returns[t] / d last_values. */
+int swarm_nstep_returns(const float* rewards, const uint8_t* dones, const float* last_values, int32_t T,
+                        int64_t n_envs, int32_t n_drones, float gamma, float* returns_out,
+                        float* coef_out, void* stream);
+
 /* -- diagnostics ---------------------------------------------------------------------------- */
 /* Synchronises `stream`, reads the sticky device error word; clears it when clear != 0. */
 int swarm_device_error(SwarmEnv* env, int32_t* code_out, int clear, void* stream);

@@ -1,0 +1,89 @@
+// swarm_a2c.cuh — the device steps of the batched A2C rollout loop that sit either side of the env step.
+//   sample_actions_kernel   softmax + Categorical(probs).sample() of A2C/train.py:66-73 for every (env, drone) pair,
+//                           written straight in the env's action layout uint8 [N][D]
+//   nstep_returns_kernel    process_rollout's reverse scan, A2C/train.py:160-183:
+//                               returns = rewards + returns * gamma * masks        (float32, this operation order, no FMA)
+//                           for every (drone, env) column of a [T] rollout, plus the product of gamma*mask factors that
+//                           the backward pass needs (d returns_t / d last_values).
+// Both are streaming kernels (bound by HBM); neither is on the env-step path.
+#pragma once
+#include "swarm_common.cuh"
+
+namespace swarm {
+
+// logits float32 [D][N][A] (the stacked policy heads' output), actions uint8 [N][D].
+// One thread per env: for every drone it reads the A logits (one 128-bit load when A == 4; consecutive threads read
+// consecutive envs, so the loads coalesce), draws u from Philox4x32-10 keyed by (seed; global env id, step, drone / 4) and
+// inverts the CDF of softmax(logits):  a = #{k : cum_k <= u * sum}  with cum_k = sum_{j<=k} exp(l_j - max).
+template <int A>
+__global__ void __launch_bounds__(256) sample_actions_kernel(const float* __restrict__ logits, int D, long long N, int Art, uint32_t seed_lo,
+                                                             uint32_t seed_hi, uint32_t step, long long env_id_base,
+                                                             uint8_t* __restrict__ actions) {
+  const int na = A ? A : Art;
+  for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (long long)gridDim.x * blockDim.x) {
+    const unsigned long long gid = (unsigned long long)(env_id_base + n);
+    uint4 r = make_uint4(0, 0, 0, 0);
+    uint32_t word = 0;
+    for (int d = 0; d < D; ++d) {
+      if ((d & 3) == 0) r = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), step, (uint32_t)(d >> 2)), seed_lo, seed_hi);
+      const uint32_t bits = (d & 3) == 0 ? r.x : ((d & 3) == 1 ? r.y : ((d & 3) == 2 ? r.z : r.w));
+      const float u = (float)(bits >> 8) * (1.0f / 16777216.0f);   // [0, 1)
+      const float* l = logits + ((size_t)d * (size_t)N + (size_t)n) * na;
+      int a = 0;
+      if constexpr (A == 4) {
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(l));
+        const float m = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+        const float e0 = expf(v.x - m), e1 = expf(v.y - m), e2 = expf(v.z - m), e3 = expf(v.w - m);
+        const float c0 = e0, c1 = __fadd_rn(c0, e1), c2 = __fadd_rn(c1, e2), c3 = __fadd_rn(c2, e3);
+        const float thr = __fmul_rn(u, c3);
+        a = (c0 <= thr) + (c1 <= thr) + (c2 <= thr);
+      } else {
+        float m = l[0];
+        for (int k = 1; k < na; ++k) m = fmaxf(m, l[k]);
+        float sum = 0.f;
+        for (int k = 0; k < na; ++k) sum = __fadd_rn(sum, expf(l[k] - m));
+        const float thr = __fmul_rn(u, sum);
+        float cum = 0.f;
+        for (int k = 0; k < na - 1; ++k) {
+          cum = __fadd_rn(cum, expf(l[k] - m));
+          a += (cum <= thr);
+        }
+      }
+      if ((D & 3) == 0) {   // four actions per 32-bit store (N*D is then a multiple of 4 and the row is 4 B aligned)
+        word |= (uint32_t)a << (8 * (d & 3));
+        if ((d & 3) == 3) {
+          *reinterpret_cast<uint32_t*>(actions + (size_t)n * D + (d - 3)) = word;
+          word = 0;
+        }
+      } else {
+        actions[(size_t)n * D + d] = (uint8_t)a;
+      }
+    }
+  }
+}
+
+// rewards float32 [T][N], dones uint8 [T][N] (mask = 1 - done, A2C/train.py:95-97), last_values float32 [D][N] (the
+// bootstrap values, train.py:109-119), returns float32 [T][D][N], coef float32 [T][N] = prod_{s >= t} gamma * mask_s.
+// One thread per (drone, env) column, env fastest: every access of a warp is a contiguous 128 B line.
+__global__ void __launch_bounds__(256) nstep_returns_kernel(const float* __restrict__ rewards, const uint8_t* __restrict__ dones,
+                                                            const float* __restrict__ last_values, int T, long long N, int D, float gamma,
+                                                            float* __restrict__ returns, float* __restrict__ coef) {
+  const long long total = (long long)D * N;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long d = i / N, n = i - d * N;
+    float ret = last_values[i];
+    float c = 1.0f;
+    for (int t = T - 1; t >= 0; --t) {
+      const float mask = 1.0f - (float)dones[(size_t)t * N + n];
+      // train.py:174  returns = rewards + returns * args.gamma * masks   (left to right, each product rounded to float32)
+      ret = __fadd_rn(rewards[(size_t)t * N + n], __fmul_rn(__fmul_rn(ret, gamma), mask));
+      __stcs(returns + ((size_t)t * D + d) * N + n, ret);
+      if (d == 0 && coef) {
+        c = __fmul_rn(__fmul_rn(c, gamma), mask);
+        coef[(size_t)t * N + n] = c;
+      }
+    }
+  }
+}
+
+}  // namespace swarm

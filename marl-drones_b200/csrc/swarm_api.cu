@@ -7,6 +7,7 @@
 
 #include "../../include/swarm_b200.h"
 #include "swarm_kernels.cuh"
+#include "swarm_a2c.cuh"
 
 using namespace swarm;
 
@@ -506,3 +507,45 @@ extern "C" int swarm_device_error(SwarmEnv* e, int32_t* code_out, int clear, voi
 }
 
 extern "C" int64_t swarm_launch_count(const SwarmEnv* e) { return e ? e->launches : 0; }
+
+// ------------------------------------------------------------------------------------------------ A2C rollout helpers
+// Stateless (no handle): they work on caller-owned device buffers of the CURRENT device.
+static int current_sm_count(int* sms) {
+  int dev = -1, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return SWARM_ERR_NO_DEVICE; }
+  CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) return SWARM_ERR_NO_DEVICE;
+  CUDA_TRY(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
+  return SWARM_OK;
+}
+
+extern "C" int swarm_sample_actions(const float* logits, int32_t n_drones, int64_t n_envs, int32_t n_actions, uint64_t seed,
+                                    uint32_t step, int64_t env_id_base, uint8_t* actions_out, void* stream) {
+  if (!logits || !actions_out || n_drones < 1 || n_envs < 1 || n_actions < 1 || n_actions > 256) return SWARM_ERR_INVALID_ARG;
+  if (n_actions == 4 && (((uintptr_t)logits) & 15) != 0) return SWARM_ERR_INVALID_ARG;
+  int sms = 0;
+  int rc = current_sm_count(&sms);
+  if (rc) return rc;
+  long long b = (n_envs + 255) / 256;
+  if (b > (long long)sms * 8) b = (long long)sms * 8;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_actions == 4)
+    sample_actions_kernel<4><<<(int)b, 256, 0, st>>>(logits, n_drones, n_envs, 4, (uint32_t)seed, (uint32_t)(seed >> 32), step, env_id_base, actions_out);
+  else
+    sample_actions_kernel<0><<<(int)b, 256, 0, st>>>(logits, n_drones, n_envs, n_actions, (uint32_t)seed, (uint32_t)(seed >> 32), step, env_id_base, actions_out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_nstep_returns(const float* rewards, const uint8_t* dones, const float* last_values, int32_t T, int64_t n_envs,
+                                   int32_t n_drones, float gamma, float* returns_out, float* coef_out, void* stream) {
+  if (!rewards || !dones || !last_values || !returns_out || T < 1 || n_envs < 1 || n_drones < 1) return SWARM_ERR_INVALID_ARG;
+  int sms = 0;
+  int rc = current_sm_count(&sms);
+  if (rc) return rc;
+  long long b = ((long long)n_envs * n_drones + 255) / 256;
+  if (b > (long long)sms * 8) b = (long long)sms * 8;
+  nstep_returns_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(rewards, dones, last_values, T, n_envs, n_drones, gamma, returns_out, coef_out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}

@@ -98,6 +98,8 @@ def lib():
         "swarm_greedy_actions": (C.c_int, [vp, vp, vp]),
         "swarm_device_error": (C.c_int, [vp, C.POINTER(i32), C.c_int, vp]),
         "swarm_launch_count": (i64, [vp]),
+        "swarm_sample_actions": (C.c_int, [vp, i32, i64, i32, C.c_uint64, C.c_uint32, i64, vp, vp]),
+        "swarm_nstep_returns": (C.c_int, [vp, vp, vp, i32, i64, i32, C.c_float, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -111,7 +113,8 @@ def lib():
 EXPORTED = ("swarm_abi_version swarm_strerror swarm_last_cuda_error swarm_device_count swarm_create swarm_destroy "
             "swarm_get_config swarm_obs_elems swarm_obs_bytes swarm_state_ptr swarm_reset swarm_set_state swarm_get_state "
             "swarm_step swarm_rollout swarm_step_host swarm_stage_move swarm_stage_scatter swarm_stage_reward "
-            "swarm_stage_obs swarm_greedy_actions swarm_device_error swarm_launch_count").split()
+            "swarm_stage_obs swarm_greedy_actions swarm_device_error swarm_launch_count swarm_sample_actions "
+            "swarm_nstep_returns").split()
 
 
 def check(status):

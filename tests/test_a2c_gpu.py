@@ -1,0 +1,150 @@
+"""GPU: the batched A2C rollout loop (swarm_b200.a2c + swarm_sample_actions / swarm_nstep_returns of libswarm_b200.so) against
+the numpy oracle and against traces of the unmodified reference `train()` (tests/golden/a2c/, A2C/train.py:35-157).
+
+Bars: the env trajectory (obs, rewards, dones) and the return scan are bit-exact; quantities that pass through float32
+GEMMs / autograd (loss, gradients, updated weights) within 1e-4 relative to the tensor's scale (summation order differs
+between the reference's D batch-1 passes and one stacked pass)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import a2c_common as ac
+from oracle import a2c_oracle
+from swarm_b200 import BatchedDroneEnv
+from swarm_b200.a2c import A2CTrainer, BatchedPolicy, nstep_returns, sample_actions
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def load(name):
+    z = np.load(os.path.join(ac.A2C_GOLDEN, name + ".npz"))
+    return {k: z[k] for k in z.files}
+
+
+def test_nstep_returns_kernel_bit_exact_and_differentiable():
+    g = load("rollout_scan")
+    rs = np.random.RandomState(3)
+    cases = [(g["rewards"], g["dones"], g["last"], float(g["gamma"]), g["returns"])]
+    T, D, N = 25, 8, 1000                                                     # ragged N (not a multiple of the block size)
+    cases.append((rs.randint(-2, 131, (T, N)).astype(np.float32), (rs.rand(T, N) < 0.1).astype(np.uint8),
+                  rs.randn(D, N).astype(np.float32), 0.99, None))
+    for rew, done, last, gamma, want in cases:
+        ret_o, coef_o = a2c_oracle.nstep_returns_np(rew, done, last, gamma)
+        if want is not None:
+            assert np.array_equal(ret_o, want)
+        lv = torch.from_numpy(last).to(DEV).requires_grad_(True)
+        ret = nstep_returns(torch.from_numpy(rew).to(DEV), torch.from_numpy(done).to(DEV), lv, gamma)
+        assert np.array_equal(ret.detach().cpu().numpy(), ret_o)              # bit-exact float32
+        w = torch.from_numpy(rs.randn(*ret_o.shape).astype(np.float32)).to(DEV)
+        (ret * w).sum().backward()
+        want_grad = (w.cpu().numpy() * coef_o[:, None, :]).sum(0)
+        assert np.allclose(lv.grad.cpu().numpy(), want_grad, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("D,N,A", [(8, 4096, 4), (3, 1001, 4), (5, 257, 6), (1, 33, 2)])
+def test_sample_actions_matches_oracle(D, N, A):
+    rs = np.random.RandomState(D * 7 + A)
+    logits = (rs.randn(D, N, A) * 2).astype(np.float32)
+    want, margin = a2c_oracle.sample_actions_np(logits, seed=0x1234567855, step=9, env_id_base=1 << 33)
+    got = sample_actions(torch.from_numpy(logits).to(DEV), seed=0x1234567855, step=9, env_id_base=1 << 33).cpu().numpy()
+    assert got.shape == (N, D) and got.dtype == np.uint8 and got.max() < A
+    bad = got != want
+    assert not (bad & (margin > 1e-5)).any(), "device and oracle draws may differ only on a CDF edge (exp rounding)"
+    assert bad.mean() < 1e-3
+    # a different step or env id base gives a different stream
+    other = sample_actions(torch.from_numpy(logits).to(DEV), seed=0x1234567855, step=10, env_id_base=1 << 33).cpu().numpy()
+    if N * D >= 1000:
+        assert (other != got).mean() > 0.2
+
+
+def test_sample_actions_distribution():
+    p = np.array([0.05, 0.15, 0.3, 0.5], np.float32)
+    logits = torch.from_numpy(np.tile(np.log(p), (4, 50000, 1))).to(DEV)
+    a = sample_actions(logits, seed=1, step=0).cpu().numpy()
+    freq = np.bincount(a.reshape(-1), minlength=4) / a.size
+    assert np.abs(freq - p).max() < 5e-3
+
+
+def _trainer_from_golden(g, grad_norm_limit):
+    grid, D, N, T, seed = (int(v) for v in g["meta"])
+    env = BatchedDroneEnv(N, row_count=grid, col_count=grid, n_anamolous=5, n_drones=D, step_size=1.0, obs_mode="full",
+                          auto_reset=True, seed=1)
+    env.set_state(grid=np.stack([g[f"grid0_{n}"] for n in range(N)]), pos=np.stack([g[f"pos0_{n}"] for n in range(N)]).astype(np.float32),
+                  t=np.zeros(N, np.int32))
+    sh = ac.policy_shapes(grid * grid, D)
+    pol = BatchedPolicy(grid * grid, D, 4, device=DEV).load_reference([ac.ref_weights(seed + i, sh) for i in range(D)])
+    tr = A2CTrainer(env, pol, rollout_steps=T, lr=2e-4, gamma=0.99, grad_norm_limit=grad_norm_limit, reset_each_rollout=False)
+    tr._obs = env.stage_obs()
+    actions = torch.from_numpy(np.stack([g[f"actions_{n}"] for n in range(N)], axis=1)).to(DEV)   # [T, N, D]
+    return env, pol, tr, actions, (grid, D, N, T)
+
+
+def _close(got, want, scale, tol=1e-4):
+    return np.abs(np.asarray(got) - np.asarray(want)).max() <= tol * max(scale, 1e-6)
+
+
+def test_one_env_iteration_equals_reference_train():
+    """N = 1: rollout, loss, clipped gradients and the AdamW-updated weights equal one outer iteration of the reference."""
+    g = load("train_5x5_d2_n1")
+    env, pol, tr, actions, (grid, D, N, T) = _trainer_from_golden(g, float(g["grad_norm_limit"]))
+    logits, values, final_values = tr.rollout(actions)
+    assert np.array_equal(tr._rew.cpu().numpy()[:, 0], g["rewards_0"].astype(np.float32))
+    assert np.array_equal(tr._done.cpu().numpy()[:, 0], g["dones_0"])
+    assert np.array_equal(env.stage_obs().cpu().numpy()[0], g["obs_0"][-1].astype(np.float32))
+    loss, norms = tr.backward(logits, values, final_values)
+    assert abs(float(loss) - float(g["loss_0"])) < 1e-4 * abs(float(g["loss_0"]))
+    keys = [str(k) for k in g["keys"]]
+    for i in range(D):
+        # the reference's clip_grad_norm_ had clip_coef < 1 iff the norm exceeded the limit; the recorded norm is post-clip
+        gd = pol.reference_grad_dict(i)
+        want = g[f"grad_0_{i}"]
+        scale = np.abs(want[:, 3]).max()
+        for k, w in zip(keys, want):
+            assert _close(ac.digest(gd[k])[[0, 1, 3, 4, 5, 6, 7]], w[[0, 1, 3, 4, 5, 6, 7]], max(scale, abs(w[1]))), (i, k)
+    tr.opt.step()
+    for i in range(D):
+        sd = pol.reference_state_dict(i)
+        for k, w in zip(keys, g[f"weight_0_{i}"]):
+            # weights move by ~lr per step: compare the first entries at 1e-6 absolute (an lr-sized error would be 2e-4)
+            assert np.abs(ac.digest(sd[k])[4:] - w[4:]).max() < 2e-6, (i, k)
+            assert abs(ac.digest(sd[k])[0] - w[0]) < 1e-4 * max(1.0, w[1]), (i, k)
+    env.close()
+
+
+def test_batched_gradient_is_mean_of_independent_reference_runs():
+    """N = 3 envs from the same weights: the batched (unclipped) gradient is the mean of three reference train() iterations."""
+    g = load("train_6x6_d3_n3")
+    env, pol, tr, actions, (grid, D, N, T) = _trainer_from_golden(g, float(g["grad_norm_limit"]))
+    logits, values, final_values = tr.rollout(actions)
+    for n in range(N):
+        assert np.array_equal(tr._rew.cpu().numpy()[:, n], g[f"rewards_{n}"].astype(np.float32))
+        assert np.array_equal(tr._done.cpu().numpy()[:, n], g[f"dones_{n}"])
+    loss, _ = tr.backward(logits, values, final_values)
+    want_loss = np.mean([float(g[f"loss_{n}"]) for n in range(N)])
+    assert abs(float(loss) - want_loss) < 1e-4 * abs(want_loss)
+    keys = [str(k) for k in g["keys"]]
+    lin = [0, 4, 5, 6, 7, 8, 9, 10, 11]                                       # digest entries that are linear in the tensor
+    for i in range(D):
+        want = np.mean([g[f"grad_{n}_{i}"] for n in range(N)], axis=0)
+        scale = max(np.abs(g[f"grad_{n}_{i}"][:, 3]).max() for n in range(N))
+        gd = pol.reference_grad_dict(i)
+        for k, w in zip(keys, want):
+            assert _close(ac.digest(gd[k])[lin], w[lin], max(scale, np.abs(w[lin]).max())), (i, k)
+    env.close()
+
+
+def test_sampled_training_runs_and_learns_signal():
+    """The full loop with on-device sampling at a cfg4-like shape: finite loss, weights move, launches counted."""
+    env = BatchedDroneEnv(512, row_count=10, col_count=10, n_drones=8, step_size=1.0, obs_mode="full", auto_reset=True, seed=3)
+    tr = A2CTrainer(env, rollout_steps=5, seed=11)
+    before = tr.policy.dense1__weight.detach().clone()
+    l0 = env.launch_count
+    losses = [float(tr.train_iteration()) for _ in range(3)]
+    assert all(np.isfinite(losses))
+    assert (tr.policy.dense1__weight.detach() - before).abs().max() > 0
+    assert env.launch_count - l0 >= 3 * 5
+    assert tr._act.max() < 4 and env.device_error() == 0
+    env.close()
