@@ -336,6 +336,10 @@ def main():
     n_act = acts.shape[0]
     stream = torch.cuda.current_stream(dev)
     side = torch.cuda.Stream(dev) if world > 1 else None
+    comm = None
+    if world > 1:
+        from swarm_b200 import StatsComm
+        comm = StatsComm()
     snaps = [torch.zeros(8, dtype=torch.int64, device=dev) for _ in range(n_act)]
 
     def one_step(i, ev=None):
@@ -351,7 +355,7 @@ def main():
             snap.copy_(envs[s].stats, non_blocking=True)
             side.wait_stream(cur)
             with torch.cuda.stream(side):
-                dist.all_reduce(snap)
+                comm.allreduce(snap)        # swarm_stats_allreduce: ncclAllReduce(SUM, int64[8]) on the library's communicator
 
     for i in range(W):
         one_step(i)
@@ -528,6 +532,8 @@ def main():
         torch.cuda.synchronize(dev)
     for e in envs:
         e.close()
+    if comm is not None:
+        comm.close()
     sys.stdout.flush(); sys.stderr.flush()
     os._exit(0)
 

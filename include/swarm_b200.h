@@ -188,6 +188,18 @@ int swarm_nstep_returns(const float* rewards, const uint8_t* dones, const float*
                         int64_t n_envs, int32_t n_drones, float gamma, float* returns_out,
                         float* coef_out, void* stream);
 
+/* -- the path's one collective: episode statistics over NCCL --------------------- */
+/* libnccl.so.2 is bound with dlopen at first use (the process's own copy, e.g. PyTorch's); no link-time dependency.
+ * `comm` is an ncclComm_t passed as void*: either one the caller already owns, or one made here:
+ * rank 0 calls swarm_comm_unique_id (ncclGetUniqueId, 128 bytes), ships the bytes to every rank out of band
+ * (e.g. torch.distributed.broadcast_object_list), and every rank calls swarm_comm_init on its own device. */
+int swarm_comm_unique_id(uint8_t* id_out_128);
+int swarm_comm_init(const uint8_t* id_128, int32_t rank, int32_t world, void** comm_out);
+int swarm_comm_destroy(void* comm);
+/* ncclAllReduce(SUM, int64[8]) in place on `stats` (device; NULL = the handle's internal statistics used by
+ * swarm_step_host), enqueued on `stream`; integer sums, so the result does not depend on the reduction order. */
+int swarm_stats_allreduce(SwarmEnv* env, int64_t* stats, void* comm, void* stream);
+
 /* -- diagnostics ---------------------------------------------------------------------------- */
 /* Synchronises `stream`, reads the sticky device error word; clears it when clear != 0. */
 int swarm_device_error(SwarmEnv* env, int32_t* code_out, int clear, void* stream);

@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <dlfcn.h>
 #include <new>
 
 #include "../../include/swarm_b200.h"
@@ -548,4 +549,85 @@ extern "C" int swarm_nstep_returns(const float* rewards, const uint8_t* dones, c
   nstep_returns_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(rewards, dones, last_values, T, n_envs, n_drones, gamma, returns_out, coef_out);
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ NCCL (statistics only)
+// The path's one collective: ncclAllReduce(SUM, int64[8]) of the episode statistics, 64 B per rank.  libnccl is
+// bound at run time (dlopen of the copy the process already carries — PyTorch's — else the system one), so the library has no
+// link-time NCCL dependency and single-GPU users never load it.
+namespace {
+struct NcclId128 { char b[128]; };   // ncclUniqueId (NCCL_UNIQUE_ID_BYTES = 128), passed by value
+struct NcclApi {
+  void* handle = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, NcclId128, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl() {
+  if (g_nccl.handle) return SWARM_OK;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) { snprintf(g_cuda_err, sizeof(g_cuda_err), "dlopen(libnccl.so.2): %s", dlerror()); return SWARM_ERR_NCCL; }
+  g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
+  g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
+  g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(h, "ncclAllReduce");
+  g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "libnccl lacks a required symbol");
+    return SWARM_ERR_NCCL;
+  }
+  g_nccl.handle = h;
+  return SWARM_OK;
+}
+
+int nccl_fail(const char* what, int rc) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", what, g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error");
+  return SWARM_ERR_NCCL;
+}
+constexpr int kNcclInt64 = 4, kNcclSum = 0;   // ncclDataType_t / ncclRedOp_t values of nccl.h (stable since NCCL 2.0)
+}  // namespace
+
+extern "C" int swarm_comm_unique_id(uint8_t* id_out) {
+  if (!id_out) return SWARM_ERR_INVALID_ARG;
+  int rc = load_nccl();
+  if (rc) return rc;
+  int n = g_nccl.GetUniqueId(id_out);
+  return n ? nccl_fail("ncclGetUniqueId", n) : SWARM_OK;
+}
+
+extern "C" int swarm_comm_init(const uint8_t* id, int32_t rank, int32_t world, void** comm_out) {
+  if (!id || !comm_out || world < 1 || rank < 0 || rank >= world) return SWARM_ERR_INVALID_ARG;
+  int rc = load_nccl();
+  if (rc) return rc;
+  NcclId128 u;
+  memcpy(u.b, id, 128);
+  void* comm = nullptr;
+  int n = g_nccl.CommInitRank(&comm, world, u, rank);   // on the CURRENT CUDA device
+  if (n) return nccl_fail("ncclCommInitRank", n);
+  *comm_out = comm;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_comm_destroy(void* comm) {
+  if (!comm) return SWARM_ERR_INVALID_ARG;
+  int rc = load_nccl();
+  if (rc) return rc;
+  int n = g_nccl.CommDestroy(comm);
+  return n ? nccl_fail("ncclCommDestroy", n) : SWARM_OK;
+}
+
+extern "C" int swarm_stats_allreduce(SwarmEnv* e, int64_t* stats, void* comm, void* stream) {
+  if (!comm || (!e && !stats)) return SWARM_ERR_INVALID_ARG;
+  int rc = load_nccl();
+  if (rc) return rc;
+  if (e && (rc = use_device(e))) return rc;
+  void* buf = stats ? (void*)stats : (void*)e->stats_dev;
+  int n = g_nccl.AllReduce(buf, buf, SWARM_STAT_COUNT, kNcclInt64, kNcclSum, comm, (cudaStream_t)stream);
+  return n ? nccl_fail("ncclAllReduce", n) : SWARM_OK;
 }

@@ -5,13 +5,14 @@ Public surface:
   DroneEnv          single-env 3-tuple facade, A2C reward (reference: A2C/noVis_sim.py:7-175)
   DQLDroneEnv       same with the DQL reward tail (reference: DQL_model/noVis_sim.py:138-148)
   make_sharded_env  this rank's contiguous shard of a global env batch (no data-path collective); reduce_stats = the one
-                    collective (int64[8] statistics all-reduce)
+                    collective (int64[8] statistics all-reduce); StatsComm = the same through
+                    the library's own NCCL communicator (swarm_stats_allreduce)
   build()           compile csrc/ for sm_100a into swarm_b200/libswarm_b200.so
 """
 from ._lib import SwarmConfig, SwarmError, build, lib  # noqa: F401
 from .batched import BatchedDroneEnv  # noqa: F401
 from .facade import DQLDroneEnv, DroneEnv  # noqa: F401
-from .sharding import make_sharded_env, reduce_stats, shard_range  # noqa: F401
+from .sharding import StatsComm, make_sharded_env, reduce_stats, shard_range  # noqa: F401
 
 __all__ = ["BatchedDroneEnv", "DroneEnv", "DQLDroneEnv", "SwarmConfig", "SwarmError", "build", "lib", "make_sharded_env",
-           "reduce_stats", "shard_range"]
+           "reduce_stats", "shard_range", "StatsComm"]

@@ -15,7 +15,7 @@ SO_PATH = os.environ.get("SWARM_B200_SO") or os.path.join(_HERE, "libswarm_b200.
 HEADER = os.path.join(_REPO, "include", "swarm_b200.h")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC"]
+              "-shared", "-Xcompiler", "-fPIC", "-ldl"]
 
 REWARD_A2C, REWARD_DQL = 0, 1
 OBS_FULL, OBS_WINDOW = 0, 1
@@ -98,6 +98,10 @@ def lib():
         "swarm_greedy_actions": (C.c_int, [vp, vp, vp]),
         "swarm_device_error": (C.c_int, [vp, C.POINTER(i32), C.c_int, vp]),
         "swarm_launch_count": (i64, [vp]),
+        "swarm_comm_unique_id": (C.c_int, [vp]),
+        "swarm_comm_init": (C.c_int, [vp, i32, i32, C.POINTER(vp)]),
+        "swarm_comm_destroy": (C.c_int, [vp]),
+        "swarm_stats_allreduce": (C.c_int, [vp, vp, vp, vp]),
         "swarm_sample_actions": (C.c_int, [vp, i32, i64, i32, C.c_uint64, C.c_uint32, i64, vp, vp]),
         "swarm_nstep_returns": (C.c_int, [vp, vp, vp, i32, i64, i32, C.c_float, vp, vp, vp]),
     }
@@ -114,13 +118,13 @@ EXPORTED = ("swarm_abi_version swarm_strerror swarm_last_cuda_error swarm_device
             "swarm_get_config swarm_obs_elems swarm_obs_bytes swarm_state_ptr swarm_reset swarm_set_state swarm_get_state "
             "swarm_step swarm_rollout swarm_step_host swarm_stage_move swarm_stage_scatter swarm_stage_reward "
             "swarm_stage_obs swarm_greedy_actions swarm_device_error swarm_launch_count swarm_sample_actions "
-            "swarm_nstep_returns").split()
+            "swarm_nstep_returns swarm_comm_unique_id swarm_comm_init swarm_comm_destroy swarm_stats_allreduce").split()
 
 
 def check(status):
     if status != 0:
         L = lib()
         msg = L.swarm_strerror(status).decode()
-        if status == -3:
+        if status in (-3, -6):
             msg += ": " + L.swarm_last_cuda_error().decode()
         raise SwarmError(f"swarm_b200 error {status}: {msg}")

@@ -247,14 +247,14 @@ def a2c_loss(logits, values, returns, value_coeff=0.5, entropy_coeff=0.01):
     """A2C/train.py:121-135 per env, averaged over envs.  logits [T, D, N, A], values / returns [T, D, N].
 
     The reference's quirks are kept: the policy term multiplies the log-probabilities of ALL actions by the advantage
-    (`log_action_probs = log_probs.clone()`, train.py:125), the advantage is not detached, and the entropy term enters with
-    a plus sign.  Every reference mean runs over T*D rows (x A columns) of one env; the extra mean over N envs makes the
+    (`log_action_probs = log_probs.clone()`, train.py:125; `Variable(advantages)` detaches it there, so the critic learns from
+    the value term only), and the entropy term enters with a plus sign.  Every reference mean runs over T*D rows (x A columns) of one env; the extra mean over N envs makes the
     batched gradient the average of N independent reference runs.
     """
     advantages = returns - values                                          # train.py:178
     log_probs = F.log_softmax(logits, dim=-1)
     probs = F.softmax(logits, dim=-1)
-    policy_loss = (-log_probs * advantages.unsqueeze(-1)).mean()
+    policy_loss = (-log_probs * advantages.detach().unsqueeze(-1)).mean()   # Variable(advantages) detaches (legacy constructor)
     value_loss = advantages.pow(2).mean()
     entropy_loss = (-log_probs * probs).mean()
     return policy_loss + value_loss * value_coeff + entropy_loss * entropy_coeff

@@ -202,3 +202,21 @@ def test_sharding_invariance_on_one_gpu():
     assert torch.equal(tot, full.stats)
     for first, count, e in shards:
         assert torch.equal(e.pos, full.pos[first:first + count]) and torch.equal(e.meta, full.meta[first:first + count])
+
+
+def test_stats_allreduce_through_library_communicator():
+    """swarm_comm_* + swarm_stats_allreduce on a world of one rank (the N > 1 case runs under torchrun in bench.py --gpus N):
+    the NCCL call path works, is stream-ordered and leaves a single rank's statistics unchanged."""
+    from swarm_b200 import BatchedDroneEnv, StatsComm
+    env = BatchedDroneEnv(64, row_count=8, col_count=8, n_drones=4, step_size=1.0, seed=5)
+    a = torch.randint(0, 4, (64, 4), dtype=torch.uint8, device="cuda")
+    for _ in range(5):
+        env.step(a)
+    want = env.stats.clone()
+    comm = StatsComm()
+    assert comm.world == 1
+    got = comm.allreduce(env.stats.clone())
+    torch.cuda.synchronize()
+    assert torch.equal(got, want) and int(want[0]) == 5 * 64
+    comm.close()
+    env.close()
