@@ -2,6 +2,7 @@
 // There is NO CPU fallback: without an sm_100 device swarm_create returns SWARM_ERR_NO_DEVICE.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
 #include <new>
@@ -18,7 +19,7 @@ struct SwarmEnv {
   int ts;                 // tile size (lanes per env) of the staged warp kernel
   int staged;             // 1: swarm_warp.cuh kernel (grid staged in shared memory), 0: swarm_cta.cuh (one CTA per env)
   int wpb;                // warps per block of the staged kernel
-  int resident[2];        // resident CTAs of the staged kernel on this device ([0] generic, [1] FAST instantiation); 0 = not yet queried
+  int resident[3];        // resident CTAs of the staged kernel on this device ([0] generic, [1] FAST, [2] LEAN instantiation); 0 = not yet queried
   int sm_count;
   long long launches;
   unsigned long long* stats_dev;   // int64[8] internal statistics
@@ -273,10 +274,10 @@ extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* 
 // ------------------------------------------------------------------------------------------------ launches
 // One instantiation of the staged kernel: raises its dynamic shared-memory limit once per handle, sizes the persistent
 // grid from the occupancy calculator (resident CTAs only) and launches.
-template <int TS, typename OT, int MODE, int WC, bool FAST>
+template <int TS, typename OT, int MODE, int WC, bool FAST, bool LEAN = false>
 static cudaError_t launch_warp_inst(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks_needed, int smem) {
-  auto kernel = step_warp_kernel<TS, OT, MODE, WC, FAST>;
-  int& resident = e->resident[FAST ? 1 : 0];
+  auto kernel = step_warp_kernel<TS, OT, MODE, WC, FAST, LEAN>;
+  int& resident = e->resident[LEAN ? 2 : (FAST ? 1 : 0)];
   if (resident == 0) {
     cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (err != cudaSuccess) return err;
@@ -295,10 +296,18 @@ static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st
   const DevParams& p = e->p;
   // FAST: every stage in one pass, uint8 actions, cd <= 0.5, no dwell — the swarm_step / swarm_rollout production path
   const bool fast = (io.flags & F_ALL) == F_ALL && io.act_dtype == SWARM_ACT_U8 && p.cd_fast && !p.has_wait;
-  if (p.obs_mode == SWARM_OBS_FULL)
+  // LEAN: the FAST kernel with the tail / rollout / alignment bookkeeping folded away (see step_warp_kernel)
+  const int epc = e->wpb * (32 / TS);
+  const bool lean = fast && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epc == 0 &&
+                    ((((uintptr_t)io.actions) | ((uintptr_t)io.obs_out)) & 15) == 0 && !getenv("SWARM_NO_LEAN");
+  if (p.obs_mode == SWARM_OBS_FULL) {
+    if (lean) return launch_warp_inst<TS, OT, 0, 0, true, true>(e, io, st, blocks, smem);
     return fast ? launch_warp_inst<TS, OT, 0, 0, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, OT, 0, 0, false>(e, io, st, blocks, smem);
-  if (p.W == 5)
+  }
+  if (p.W == 5) {
+    if (lean) return launch_warp_inst<TS, OT, 1, 5, true, true>(e, io, st, blocks, smem);
     return fast ? launch_warp_inst<TS, OT, 1, 5, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, OT, 1, 5, false>(e, io, st, blocks, smem);
+  }
   return fast ? launch_warp_inst<TS, OT, 1, 0, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, OT, 1, 0, false>(e, io, st, blocks, smem);
 }
 

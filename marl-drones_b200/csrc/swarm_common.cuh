@@ -15,9 +15,6 @@
 namespace swarm {
 
 constexpr unsigned FULL = 0xffffffffu;
-#ifndef SWARM_WAIT_TICKS
-#define SWARM_WAIT_TICKS 0x989680u   // suspend-time hint of mbarrier.try_wait: the warp sleeps in hardware instead of spinning on the issue port
-#endif
 
 enum : int { F_MOVE = 1, F_SCATTER = 2, F_REWARD = 4, F_OBS = 8, F_ALL = 15 };
 
@@ -104,11 +101,11 @@ __device__ __forceinline__ void mbar_wait_s(uint32_t bar_s, uint32_t parity) {
       "{\n"
       ".reg .pred p;\n"
       "SWARM_WAITS_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
       "@p bra SWARM_DONES_%=;\n"
       "bra SWARM_WAITS_%=;\n"
       "SWARM_DONES_%=:\n"
-      "}\n" ::"r"(bar_s), "r"(parity), "r"(SWARM_WAIT_TICKS) : "memory");
+      "}\n" ::"r"(bar_s), "r"(parity) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_s(uint32_t bar_s) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_s) : "memory");

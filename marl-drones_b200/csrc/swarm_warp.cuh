@@ -167,7 +167,10 @@ __device__ __forceinline__ void emit_full_smem(const DevParams& p, const ObsCvt<
 // arithmetic even when every warp of the GPU runs in lock step.  The copies need no registers.  The grid is persistent
 // (resident CTAs only): prologue, LUT build and the statistics epilogue are paid once per warp, and the int64[8]
 // statistics cost six RED.ADD per CTA.
-template <int TS, typename OT, int MODE, int WC, bool FAST>
+// LEAN (implies FAST): additionally one step per launch (io.T == 1), N a multiple of the CTA's env count, D == TS, obs and
+// statistics requested, every per-group array on the TMA path — checked by the host (launch_warp_ts).  Folds the tail /
+// rollout / alignment bookkeeping of the group loop away; the arithmetic of the four stages is the same code.
+template <int TS, typename OT, int MODE, int WC, bool FAST, bool LEAN = false>
 __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
   constexpr int EPW = 32 / TS;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -179,7 +182,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   const int flags = FAST ? (F_ALL | (io.flags & F_RESET)) : io.flags;
   const bool cd_fast = FAST ? true : (p.cd_fast != 0);
   const bool has_wait = FAST ? false : (p.has_wait != 0);
-  const bool want_stats = io.stats != nullptr && (flags & F_REWARD);
+  const bool want_stats = LEAN ? true : (io.stats != nullptr && (flags & F_REWARD));
   const ObsCvt<OT> cvt(p);
   if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
   if constexpr (MODE == 1 && sizeof(OT) == 4) {
@@ -197,16 +200,17 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   OT* const stage = reinterpret_cast<OT*>(smem_raw + (size_t)wib * p.stage_bytes);   // this warp's [EPW][D][W*W] staging (WINDOW)
   unsigned char* const inbuf0 = smem_raw + (size_t)wpb * p.stage_bytes;              // two CTA input buffers of p.in_bytes each
   const int tile = lane / TS, tl = lane % TS, lead = tile * TS;
-  const int D = p.D, N = p.N, env_words = p.env_words;
+  const int D = LEAN ? TS : p.D, N = p.N, env_words = p.env_words;
+  const int T = LEAN ? 1 : io.T;
   const int ngroups = (N + EPW - 1) / EPW;
   const int EPC = wpb * EPW;                      // envs per CTA-iteration (wpb consecutive groups)
   const int ncg = (N + EPC - 1) / EPC;            // CTA-groups
-  const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
+  const bool want_obs = LEAN ? true : ((flags & F_OBS) && io.obs_out != nullptr);
   const int WW = MODE == 1 ? (WC ? WC : p.W) * (WC ? WC : p.W) : 1;
   OT* const my_stage = stage + (tile * D + tl) * WW;
   // which per-group arrays may ride the bulk copy (size and address multiples of 16 B; the grid and meta always do)
-  const bool act_tma_ok = (flags & F_MOVE) && (FAST || io.act_dtype == 0) && (((uintptr_t)io.actions) & 15) == 0;
-  const bool meta_tma = (flags & F_REWARD) != 0;
+  const bool act_tma_ok = LEAN ? true : (flags & F_MOVE) && (FAST || io.act_dtype == 0) && (((uintptr_t)io.actions) & 15) == 0;
+  const bool meta_tma = LEAN ? true : (flags & F_REWARD) != 0;
   // statistics accumulators are warp-uniform (REDUX results), so they live in uniform registers
   long long acc_rew = 0, acc_len = 0, acc_ret = 0;
   int acc_done = 0, acc_cells = 0, acc_anom = 0;
@@ -215,14 +219,14 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   // array — into input buffer `b`: four bulk copies on full_bar[b].  The partial tail CTA-group moves only its grid and
   // meta by TMA (their sizes are always multiples of 16 B) and its warps load positions / actions directly.
   const uint32_t in_s = smem_u32(inbuf0), full_s = smem_u32(&full_bar[0]), empty_s = smem_u32(&empty_bar[0]), stage_s = smem_u32(stage);
-  const bool pos_tma_c = ((EPC * D * 8) & 15) == 0;
-  const bool act_tma_c = act_tma_ok && ((EPC * D) & 15) == 0 && io.T == 1;
+  const bool pos_tma_c = LEAN ? true : ((EPC * D * 8) & 15) == 0;
+  const bool act_tma_c = LEAN ? true : (act_tma_ok && ((EPC * D) & 15) == 0 && io.T == 1);
   const uint32_t gbytes_c = (uint32_t)EPC * (uint32_t)env_words * 4u, posb_c = (uint32_t)EPC * (uint32_t)D * 8u;
   const uint32_t tx_c = gbytes_c + (pos_tma_c ? posb_c : 0u) + (meta_tma ? (uint32_t)EPC * 16u : 0u) + (act_tma_c ? (uint32_t)(EPC * D) : 0u);
   auto produce = [&](int cg, int b) {
     const int e0 = cg * EPC;
     const uint32_t dst = in_s + (uint32_t)b * (uint32_t)p.in_bytes, bs = full_s + 8u * (uint32_t)b;
-    if (e0 + EPC <= N) {
+    if (LEAN || e0 + EPC <= N) {
       mbar_expect_tx_s(bs, tx_c);
       bulk_g2s_s(dst, p.grid + (size_t)e0 * env_words, gbytes_c, bs);
       if (pos_tma_c) bulk_g2s_s(dst + p.off_pos, p.pos + (size_t)e0 * D, posb_c, bs);
@@ -249,14 +253,14 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
       produce(cg + gridDim.x, b ^ 1);
     }
     const int grp = cg * wpb + wib;
-    if (grp >= ngroups) continue;   // idle warp of the tail CTA-group (last iteration only)
+    if (!LEAN && grp >= ngroups) continue;   // idle warp of the tail CTA-group (last iteration only)
     unsigned char* const in = inbuf0 + b * p.in_bytes;
     uint32_t* const sgrid = reinterpret_cast<uint32_t*>(in) + wib * EPW * env_words;
-    const bool cta_full = cg * EPC + EPC <= N;
-    const int env0 = grp * EPW, nenv = min(EPW, N - env0);
-    const bool valid = tile < nenv;
+    const bool cta_full = LEAN ? true : (cg * EPC + EPC <= N);
+    const int env0 = grp * EPW, nenv = LEAN ? EPW : min(EPW, N - env0);
+    const bool valid = LEAN ? true : (tile < nenv);
     const int env = valid ? env0 + tile : env0;
-    const bool active = valid && tl < D;
+    const bool active = LEAN ? true : (valid && tl < D);
     uint32_t* const sg = sgrid + tile * env_words;
     uint32_t* const gg = p.grid + (size_t)env * env_words;
     const bool pos_tma = pos_tma_c && cta_full, act_tma = act_tma_c && cta_full;
@@ -277,7 +281,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     if (active && act_tma) a = (int)in[p.off_act + (wib * EPW + tile) * D + tl];
     if (valid && tl == 0 && meta_tma) m = reinterpret_cast<const int4*>(in + p.off_meta)[wib * EPW + tile];
 
-    for (int t = 0; t < io.T; ++t, aidx += (size_t)N * D, ridx += N) {
+    for (int t = 0; t < T; ++t, aidx += (size_t)N * D, ridx += N) {
       if (t > 0 && active && (flags & F_MOVE))   // rollout: positions / meta are carried in registers, actions are re-read
         a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
 
@@ -304,7 +308,10 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
             cand = dx * dx + dy * dy < p.cd2_thr;     // sqrt(d2) < collision_dist (noVis_sim.py:81)
             cell = cy * p.R + cx;
           }
-          // drones of one env on one cell form a match group; its lowest lane resolves the conflict for all of them
+          // drones of one env on one cell form a match group; its lowest lane resolves the conflict for all of them.
+          // (Measured: guarding the match with "does any lane stand on an unmapped cell", or electing the winner by the return
+          // value of a shared-memory atomicAnd instead, both make the cfg3 step 50 % SLOWER — DESIGN.md §5 — so the match is
+          // unconditional.)
           const unsigned key = cand ? (((unsigned)tile << 24) | (unsigned)cell) : (0x80000000u | (unsigned)lane);
           const unsigned mm = __match_any_sync(FULL, key);
           if (cand && lane == __ffs(mm) - 1) {
@@ -394,8 +401,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
       }
 
       // ---- stage (4): observation emission
-      if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
-        OT* obase = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * N * p.obs_per_env);
+      if (want_obs && (LEAN || !io.obs_last_only || t == T - 1)) {
+        OT* obase = reinterpret_cast<OT*>(io.obs_out) + ((LEAN || io.obs_last_only) ? (size_t)0 : (size_t)t * N * p.obs_per_env);
         if (MODE == 0) {
           emit_full_smem<OT>(p, cvt, sgrid, nenv, lane, obase + (size_t)env0 * p.RC);
         } else {
@@ -407,7 +414,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
           const int n = nenv * D * WW;
           OT* dst = obase + (size_t)env0 * D * WW;
           const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(OT);
-          if ((((uintptr_t)dst) & 15) == 0 && (bytes & 15u) == 0) {
+          if (LEAN || ((((uintptr_t)dst) & 15) == 0 && (bytes & 15u) == 0)) {
             if (lane == 0) {   // one TMA bulk store for the whole group
               bulk_s2g_s(dst, stage_s, bytes);
               bulk_commit();
@@ -435,8 +442,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     __syncthreads();
     if (threadIdx.x < 6 && s_stats[threadIdx.x] != 0ull) atomicAdd(io.stats + 2 + threadIdx.x, s_stats[threadIdx.x]);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-      atomicAdd(io.stats + 0, (unsigned long long)((long long)N * io.T));
-      atomicAdd(io.stats + 1, (unsigned long long)((long long)N * D * io.T));
+      atomicAdd(io.stats + 0, (unsigned long long)((long long)N * T));
+      atomicAdd(io.stats + 1, (unsigned long long)((long long)N * D * T));
     }
   }
 }
