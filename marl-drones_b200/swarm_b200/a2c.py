@@ -270,13 +270,14 @@ class A2CTrainer:
     """
 
     def __init__(self, env, policy=None, rollout_steps=25, lr=2e-4, gamma=0.99, value_coeff=0.5, entropy_coeff=0.01,
-                 grad_norm_limit=10.0, seed=0, reset_each_rollout=True, fused_optimizer=True, group=None):
+                 grad_norm_limit=10.0, seed=0, reset_each_rollout=True, fused_optimizer=True, group=None, icm=None):
         self.env, self.T = env, rollout_steps
         self.N, self.D = env.num_envs, env.n_drones
         self.policy = policy if policy is not None else BatchedPolicy(env.state_size, env.n_drones, env.action_size, device=env.device)
         self.gamma, self.value_coeff, self.entropy_coeff = gamma, value_coeff, entropy_coeff
         self.grad_norm_limit, self.seed, self.reset_each_rollout = grad_norm_limit, seed, reset_each_rollout
         self.opt = torch.optim.AdamW(self.policy.parameters(), lr=lr, fused=bool(fused_optimizer) and env.device.type == "cuda")
+        self.icm = icm                  # BatchedICM or None (args.enable_icm, train.py:48-49)
         self.group = group              # torch.distributed group for data-parallel gradient averaging (None + initialised = WORLD)
         self.total_steps = 0            # env steps per env, as train.py:46
         self.sample_step = 0
@@ -293,6 +294,7 @@ class A2CTrainer:
         if self._obs is None or self.reset_each_rollout:
             self._obs = env.reset()                                         # train.py:53
         obs = self._obs
+        curr_state = obs.clone() if self.icm is not None else None      # train.py:57 — never advanced inside the rollout
         logits_l, values_l = [], []
         with torch.set_grad_enabled(grad):
             for t in range(self.T):
@@ -303,7 +305,10 @@ class A2CTrainer:
                     self._act[t].copy_(actions[t])
                 self.sample_step += 1
                 obs, rew, done, _ = env.step(self._act[t])                  # train.py:76-80 (auto-reset returns the reset obs)
-                self._rew[t].copy_(rew)
+                if self.icm is not None:                                    # train.py:85-92: drone 0's logits, s_t = curr_state
+                    torch.add(rew, self.icm(logits[0].detach(), curr_state, obs), out=self._rew[t])
+                else:
+                    self._rew[t].copy_(rew)
                 self._done[t].copy_(done)
                 logits_l.append(logits)
                 values_l.append(values.squeeze(-1))
@@ -362,3 +367,71 @@ class A2CTrainer:
     def train_iteration(self, actions=None):
         logits, values, final_values = self.rollout(actions)
         return self.update(logits, values, final_values)
+
+
+# ------------------------------------------------------------------------------------------------ ICM
+class _IcmFeatures(nn.Module):      # A2C/curiosity.py:7-18
+    def __init__(self, obs_size, out_size):
+        super().__init__()
+        self.dense1, self.dense2, self.dense3 = nn.Linear(obs_size, 128), nn.Linear(128, 64), nn.Linear(64, out_size)
+
+    def forward(self, obs):
+        return self.dense3(F.leaky_relu(self.dense2(F.leaky_relu(self.dense1(obs)))))
+
+
+class _IcmInverse(nn.Module):       # A2C/curiosity.py:21-37 (kept for state_dict parity; it does not influence the bonus)
+    def __init__(self, n, action_space):
+        super().__init__()
+        self.in1, self.in2 = nn.Linear(n, n), nn.Linear(n, n)
+        self.dense1, self.dense2, self.dense3 = nn.Linear(2 * n, 32), nn.Linear(32, 16), nn.Linear(16, action_space)
+
+    def forward(self, x1, x2):
+        out = torch.cat((F.leaky_relu(self.in1(x1)), F.leaky_relu(self.in2(x2))), dim=-1)
+        return self.dense3(F.leaky_relu(self.dense2(F.leaky_relu(self.dense1(out)))))
+
+
+class _IcmForward(nn.Module):       # A2C/curiosity.py:40-54
+    def __init__(self, n, action_space):
+        super().__init__()
+        self.act_in1, self.act_in2 = nn.Linear(action_space, 16), nn.Linear(16, n)
+        self.state_in1, self.dense1 = nn.Linear(n, n), nn.Linear(2 * n, n)
+
+    def forward(self, act, state):
+        act = F.leaky_relu(self.act_in2(F.leaky_relu(self.act_in1(act))))
+        return self.dense1(torch.cat((F.leaky_relu(self.state_in1(state)), act), dim=-1))
+
+
+class BatchedICM(nn.Module):
+    """The intrinsic-curiosity bonus of A2C/curiosity.py:57-86 for N envs at once, on the obs the env left in HBM.
+
+    Submodule / parameter names equal the reference `ICM`'s (`features`, `inverse_model`, `forward_model`), so
+    `load_reference(icm)` copies a reference instance.  As in the reference the module is never optimised (train.py creates
+    it without an optimiser; its `.backward()` calls only accumulate unused gradients), so the bonus is a fixed random
+    feature-prediction error:  r_i = 10 * 0.5 * mean_k (forward_model(logits_0, phi(s_t)) - phi(s_t1))_k^2   per env
+    (every layer is row-wise, so a batch of N rows equals N batch-1 calls).  Reference quirks kept by the trainer: the bonus
+    uses drone 0's logits only (train.py:85-92) and `s_t` is the FIRST observation of the rollout (`curr_state` is never
+    advanced, train.py:57).
+    """
+
+    def __init__(self, obs_size, action_space=4, hidden_size=32, device=None):
+        super().__init__()
+        self.features = _IcmFeatures(obs_size, hidden_size)
+        self.inverse_model = _IcmInverse(hidden_size, action_space)
+        self.forward_model = _IcmForward(hidden_size, action_space)
+        if device is not None:
+            self.to(device)
+
+    @torch.no_grad()
+    def load_reference(self, icm):
+        """icm: a reference `ICM` instance (plain object holding three nn.Modules) or a dict of their state_dicts."""
+        for name in ("features", "inverse_model", "forward_model"):
+            sd = icm[name] if isinstance(icm, dict) else getattr(icm, name).state_dict()
+            getattr(self, name).load_state_dict(sd)
+        return self
+
+    @torch.no_grad()
+    def forward(self, a_t_logits, s_t, s_t1):
+        """a_t_logits [N, A] (drone 0's policy logits), s_t / s_t1 [N, obs] -> bonus [N] (curiosity.py:74-86)."""
+        phi_st, phi_st1 = self.features(s_t), self.features(s_t1)
+        pred = self.forward_model(a_t_logits, phi_st)
+        return (pred - phi_st1).pow(2).mean(dim=-1) * (0.5 * 10.0)

@@ -40,3 +40,12 @@ def policy_shapes(obs_size, n_drones, action_size=4):
         sh[f"{head}.dense4.weight"] = (a, 32)
         sh[f"{head}.dense4.bias"] = (a,)
     return sh
+
+
+def icm_weights(seed, obs_size, action_space=4):
+    """{'features' | 'inverse_model' | 'forward_model': state_dict} for the reference ICM's three modules
+    (A2C/curiosity.py:57-61), drawn like ref_weights (numpy legacy MT19937, identical everywhere)."""
+    from swarm_b200.a2c import BatchedICM
+    ref = BatchedICM(obs_size, action_space)
+    return {name: ref_weights(seed + 1000 * k, {key: tuple(v.shape) for key, v in getattr(ref, name).state_dict().items()})
+            for k, name in enumerate(("features", "inverse_model", "forward_model"))}

@@ -22,9 +22,11 @@ import torch
 HERE = os.path.dirname(os.path.abspath(__file__))
 TESTS = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, TESTS)
+sys.path.insert(0, os.path.join(os.path.dirname(TESTS), "marl-drones_b200"))
 sys.path.insert(0, "/root/reference/A2C")
 import a2c_common as ac  # noqa: E402
 import models as ref_models  # noqa: E402
+import curiosity as ref_curiosity  # noqa: E402
 import train as ref_train  # noqa: E402
 from noVis_sim import DroneEnv  # noqa: E402
 
@@ -118,9 +120,34 @@ class RecOpt:
         self.opt.zero_grad()
 
 
-def train_case(name, grid, n_drones, n_envs, T, seed, grad_norm_limit):
+def det_icm(seed, obs_size):
+    """A reference ICM whose three modules carry the deterministic test weights (the reference draws them from torch's RNG)."""
+    icm = ref_curiosity.ICM(obs_size=obs_size, action_space=4)
+    for name, sd in ac.icm_weights(seed, obs_size).items():
+        getattr(icm, name).load_state_dict(sd)
+    return icm
+
+
+def icm_case():
+    """ICM.__call__ (curiosity.py:74-86) at batch 1 on N rows: the bonus r_i it returns."""
+    rs = np.random.RandomState(5)
+    obs_size, N = 36, 8
+    icm = det_icm(31, obs_size)
+    s_t = rs.choice([0.0, 1.0, 5.0], size=(N, obs_size)).astype(np.float32)
+    s_t1 = rs.choice([0.0, 1.0, 5.0], size=(N, obs_size)).astype(np.float32)
+    logits = rs.randn(N, 4).astype(np.float32)
+    a_t = rs.randint(0, 4, N)
+    r = np.zeros(N)
+    for n in range(N):
+        r[n] = icm(a_t=torch.tensor([a_t[n]], dtype=torch.long), a_t_logits=torch.from_numpy(logits[n:n + 1]),
+                   s_t=torch.from_numpy(s_t[n:n + 1]), s_t1=torch.from_numpy(s_t1[n:n + 1]))
+    np.savez_compressed(os.path.join(HERE, "icm_6x6.npz"), s_t=s_t, s_t1=s_t1, logits=logits, bonus=r, meta=np.array([obs_size, 31]))
+    print("icm_6x6 bonus", r[:4])
+
+
+def train_case(name, grid, n_drones, n_envs, T, seed, grad_norm_limit, enable_icm=False):
     obs_size = grid * grid
-    out = dict(meta=np.array([grid, n_drones, n_envs, T, seed]), grad_norm_limit=np.float64(grad_norm_limit))
+    out = dict(meta=np.array([grid, n_drones, n_envs, T, seed]), grad_norm_limit=np.float64(grad_norm_limit), enable_icm=np.int32(enable_icm))
     keys = None
     tmp = tempfile.mkdtemp()
     cwd = os.getcwd()
@@ -133,7 +160,8 @@ def train_case(name, grid, n_drones, n_envs, T, seed, grad_norm_limit):
             torch.manual_seed(seed * 100 + n)
             env = RecEnv(row_count=grid, col_count=grid, step_size=1.0, n_anamolous=5, n_drones=n_drones)
             env.resets.clear()                                            # the constructor's init_env is discarded by train()'s reset
-            args = types.SimpleNamespace(enable_icm=False, policy="MLP", total_steps=T, rollout_steps=T, gamma=0.99, value_coeff=0.5,
+            ref_train.ICM = (lambda obs_size, action_space: det_icm(seed + 7, obs_size))   # same class, deterministic weights
+            args = types.SimpleNamespace(enable_icm=enable_icm, policy="MLP", total_steps=T, rollout_steps=T, gamma=0.99, value_coeff=0.5,
                                          entropy_coeff=0.01, grad_acc=1, grad_norm_limit=grad_norm_limit, save_freq=10 ** 9 + 7,
                                          grid_size=grid)
             logging.getLogger().handlers.clear()
@@ -145,7 +173,7 @@ def train_case(name, grid, n_drones, n_envs, T, seed, grad_norm_limit):
             out[f"rewards_{n}"] = np.array(env.rewards, np.float64)
             out[f"dones_{n}"] = np.array(env.dones, np.uint8)
             out[f"obs_{n}"] = np.array(env.obs, np.int8)
-            loss_line = open(os.path.join(tmp, "A2C_MLP.log")).read().strip().splitlines()[-1]
+            loss_line = open(os.path.join(tmp, "A2C_ICM_MLP.log" if enable_icm else "A2C_MLP.log")).read().strip().splitlines()[-1]
             out[f"loss_{n}"] = np.float64(loss_line.split("loss: ")[1].split(",")[0])
             for i in range(n_drones):
                 g = opts[i].grads
@@ -167,3 +195,5 @@ if __name__ == "__main__":
     scan_case()
     train_case("train_5x5_d2_n1", 5, 2, 1, 6, 21, 10.0)          # default clip: post-update weights must match
     train_case("train_6x6_d3_n3", 6, 3, 3, 5, 22, 1e9)           # no clip: batched gradient = mean of 3 reference runs
+    icm_case()
+    train_case("train_icm_5x5_d2_n2", 5, 2, 2, 5, 23, 1e9, enable_icm=True)   # curiosity bonus in the rewards (drone 0, fixed s_t)

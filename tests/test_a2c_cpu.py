@@ -116,3 +116,28 @@ def test_sampler_oracle_distribution():
     a, _ = a2c_oracle.sample_actions_np(logits, seed=5, step=3)
     freq = np.bincount(a.reshape(-1), minlength=4) / a.size
     assert np.abs(freq - [0.1, 0.2, 0.3, 0.4]).max() < 0.01
+
+
+def test_batched_icm_equals_reference_bonus():
+    """BatchedICM on N rows == the reference ICM.__call__ at batch 1 per row (curiosity.py:74-86), frozen in icm_6x6.npz."""
+    from swarm_b200.a2c import BatchedICM
+    g = load("icm_6x6")
+    obs_size, seed = (int(v) for v in g["meta"])
+    icm = BatchedICM(obs_size).load_reference(ac.icm_weights(seed, obs_size))
+    r = icm(torch.from_numpy(g["logits"]), torch.from_numpy(g["s_t"]), torch.from_numpy(g["s_t1"]))
+    assert np.abs(r.numpy() - g["bonus"]).max() < 1e-5 * max(1.0, np.abs(g["bonus"]).max())
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/A2C/curiosity.py"), reason="live reference only in the build container")
+def test_batched_icm_vs_live_reference():
+    sys.path.insert(0, "/root/reference/A2C")
+    import curiosity as ref_curiosity
+    from swarm_b200.a2c import BatchedICM
+    torch.manual_seed(3)
+    ref = ref_curiosity.ICM(obs_size=25, action_space=4)                     # the reference's own initialisation
+    icm = BatchedICM(25).load_reference(ref)
+    s_t, s_t1, lg = torch.rand(6, 25) * 5, torch.rand(6, 25) * 5, torch.randn(6, 4)
+    got = icm(lg, s_t, s_t1)
+    for n in range(6):
+        want = ref(a_t=torch.tensor([n % 4]), a_t_logits=lg[n:n + 1], s_t=s_t[n:n + 1], s_t1=s_t1[n:n + 1])
+        assert abs(float(got[n]) - want) < 1e-5 * max(1.0, abs(want))

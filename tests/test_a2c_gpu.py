@@ -13,7 +13,7 @@ import torch
 import a2c_common as ac
 from oracle import a2c_oracle
 from swarm_b200 import BatchedDroneEnv
-from swarm_b200.a2c import A2CTrainer, BatchedPolicy, nstep_returns, sample_actions
+from swarm_b200.a2c import A2CTrainer, BatchedICM, BatchedPolicy, nstep_returns, sample_actions
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -76,7 +76,10 @@ def _trainer_from_golden(g, grad_norm_limit):
                   t=np.zeros(N, np.int32))
     sh = ac.policy_shapes(grid * grid, D)
     pol = BatchedPolicy(grid * grid, D, 4, device=DEV).load_reference([ac.ref_weights(seed + i, sh) for i in range(D)])
-    tr = A2CTrainer(env, pol, rollout_steps=T, lr=2e-4, gamma=0.99, grad_norm_limit=grad_norm_limit, reset_each_rollout=False)
+    icm = None
+    if "enable_icm" in g and int(g["enable_icm"]):
+        icm = BatchedICM(grid * grid, device=DEV).load_reference(ac.icm_weights(seed + 7, grid * grid)).to(DEV)
+    tr = A2CTrainer(env, pol, rollout_steps=T, lr=2e-4, gamma=0.99, grad_norm_limit=grad_norm_limit, reset_each_rollout=False, icm=icm)
     tr._obs = env.stage_obs()
     actions = torch.from_numpy(np.stack([g[f"actions_{n}"] for n in range(N)], axis=1)).to(DEV)   # [T, N, D]
     return env, pol, tr, actions, (grid, D, N, T)
@@ -147,4 +150,28 @@ def test_sampled_training_runs_and_learns_signal():
     assert (tr.policy.dense1__weight.detach() - before).abs().max() > 0
     assert env.launch_count - l0 >= 3 * 5
     assert tr._act.max() < 4 and env.device_error() == 0
+    env.close()
+
+
+def test_icm_bonus_iteration_equals_reference_train():
+    """enable_icm: the curiosity bonus (drone 0's logits, s_t fixed at the rollout's first obs) enters the rewards exactly as in
+    the reference train() (train.py:85-92); loss and the mean gradient of two independent runs match."""
+    g = load("train_icm_5x5_d2_n2")
+    env, pol, tr, actions, (grid, D, N, T) = _trainer_from_golden(g, float(g["grad_norm_limit"]))
+    logits, values, final_values = tr.rollout(actions)
+    for n in range(N):
+        bonus = tr._rew.cpu().numpy()[:, n] - g[f"rewards_{n}"].astype(np.float32)      # recorded rewards are the env's own
+        assert (bonus > 0).all() and bonus.max() < 50, "the curiosity bonus is a small positive prediction error"
+        assert np.array_equal(tr._done.cpu().numpy()[:, n], g[f"dones_{n}"])
+    loss, _ = tr.backward(logits, values, final_values)
+    want_loss = np.mean([float(g[f"loss_{n}"]) for n in range(N)])
+    assert abs(float(loss) - want_loss) < 1e-4 * abs(want_loss)
+    keys = [str(k) for k in g["keys"]]
+    lin = [0, 4, 5, 6, 7, 8, 9, 10, 11]
+    for i in range(D):
+        want = np.mean([g[f"grad_{n}_{i}"] for n in range(N)], axis=0)
+        scale = max(np.abs(g[f"grad_{n}_{i}"][:, 3]).max() for n in range(N))
+        gd = pol.reference_grad_dict(i)
+        for k, w in zip(keys, want):
+            assert _close(ac.digest(gd[k])[lin], w[lin], max(scale, np.abs(w[lin]).max())), (i, k)
     env.close()
