@@ -14,16 +14,24 @@ namespace swarm {
 
 // Stages (1)-(3) (+ auto-reset) of one env by one warp.
 // `sg`: the env's packed grid in shared memory (null = work on the HBM copy only).
-__device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc, uint32_t* sg) {
+// `pre_pk` (may be null): stages (1)-(2) were already run by the whole CTA (move_scatter_cta); *pre_pk holds the env's packed
+// coverage totals (reward | cells << 16 | anomalous << 24) and this warp runs stage (3) only.
+__device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc, uint32_t* sg,
+                                              const int* pre_pk = nullptr, float2* sp = nullptr, const int4* m_pre = nullptr) {
   constexpr int TS = 32;
-  const int flags = io.flags;
+  const int flags = pre_pk ? (io.flags & ~(F_MOVE | F_SCATTER)) : io.flags;
   const int D = p.D;
   const int nch = (D + TS - 1) / TS;
   uint32_t* g = p.grid + (size_t)env * p.env_words;
   int rew = 0, ncl = 0, nan = 0;
   float x = 0.f, y = 0.f;   // chunk-0 drone of this lane (all drones when D <= 32)
 
-  for (int c = 0; c < nch; ++c) {
+  if (pre_pk) {
+    const int pk = *pre_pk;
+    rew = pk & 0xffff; ncl = (pk >> 16) & 0xff; nan = (pk >> 24) & 0xff;
+    if (lane < D) { const float2 q = sp ? sp[lane] : __ldcg(p.pos + (size_t)env * D + lane); x = q.x; y = q.y; }
+  }
+  for (int c = 0; c < (pre_pk ? 0 : nch); ++c) {
     const int d = c * TS + lane;
     const bool active = d < D;
     float2 q = make_float2(0.f, 0.f);
@@ -84,7 +92,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
     if (lane == 0) scatter_sequential(p, env, g, sg, rew, ncl, nan);
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
+  for (int o = 16; o > 0 && !pre_pk; o >>= 1) {
     rew += __shfl_xor_sync(FULL, rew, o);
     ncl += __shfl_xor_sync(FULL, ncl, o);
     nan += __shfl_xor_sync(FULL, nan, o);
@@ -92,16 +100,16 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
 
   if (flags & F_REWARD) {   // stage (3)
     int4 m = make_int4(0, 0, 0, 0);
-    if (lane == 0) m = __ldcg(p.meta + env);
+    if (lane == 0) m = m_pre ? *m_pre : __ldcg(p.meta + env);
     const int tcount = __shfl_sync(FULL, m.x, 0);
     const bool punish = tcount > p.punish_thr;                    // noVis_sim.py:141-143 (count before increment)
     const bool need = !punish;
     bool spread = false;
     __syncwarp();   // every chunk's position stores precede the D > 32 re-reads in tile_spread
-    if (need) spread = tile_spread<TS>(p, env, 0, lane, need, x, y);
+    if (need) spread = tile_spread<TS>(p, env, 0, lane, need, x, y, sp);
     bool do_reset = false;
     if (lane == 0) {
-      int r = (flags & F_SCATTER) ? rew : io.cover_in[env];
+      int r = ((flags & F_SCATTER) || pre_pk) ? rew : io.cover_in[env];
       if (p.reward_mode == 0) r += ((!punish && spread) ? 1 : 0) - 1;   // A2C noVis_sim.py:150-152
       else r += punish ? -1 : (spread ? 1 : 0);                         // DQL noVis_sim.py:141-148
       const int rem = m.y - ncl;
@@ -121,6 +129,8 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
       reset_tile<TS>(p, env, episode + 1, lane, true);
       if (sg)   // refresh the shared-memory copy from the freshly written HBM grid
         for (int w = lane; w < p.env_words; w += 32) sg[w] = ld_grid(g + w);
+      if (sp)   // ... and the shared-memory positions from the reset ones
+        for (int d = lane; d < D; d += 32) sp[d] = __ldcg(p.pos + (size_t)env * D + d);
     }
   } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
     if (lane == 0) {
@@ -131,9 +141,44 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
   __syncwarp();
 }
 
+// Stages (1)-(2) by the WHOLE CTA for collision_dist <= 0.5 without dwell (the production path): one thread per drone moves,
+// clips and tests its nearest lattice cell on the shared-memory grid.  Several drones on one cell: the return value of the
+// shared-memory atomicAnd elects exactly one of them (the one that still saw the code), so the cell is cleared and rewarded
+// once — the per-env reward is a sum, the order does not matter.  Totals are packed into *s_pk (<= 255 drones
+// can clear a cell per step: D <= 1024 drones, but at most 255 fit the 8-bit fields — larger D fall back to the warp path).
+__device__ __forceinline__ float2 move_drone(const DevParams& p, const StepIO& io, int t, int env, int d) {   // stage (1)
+  float2* pp = p.pos + (size_t)env * p.D + d;
+  float2 q = __ldcg(pp);
+  const int a = load_action(io.actions, io.act_dtype, ((long long)t * p.N + env) * p.D + d);
+  if (a == 0) q.y -= p.ss;                      // noVis_sim.py:121-128
+  else if (a == 1) q.x += p.ss;
+  else if (a == 2) q.y += p.ss;
+  else if (a == 3) q.x -= p.ss;
+  else atomicOr(p.err, 1);
+  q.x = fminf(fmaxf(q.x, 0.f), p.xmax);         // noVis_sim.py:130-135
+  q.y = fminf(fmaxf(q.y, 0.f), p.ymax);
+  __stcg(pp, q);
+  return q;
+}
+__device__ __forceinline__ void scatter_drone(const DevParams& p, int env, float2 q, uint32_t* sg, int* s_pk) {   // stage (2)
+  const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
+  const double dx = (double)cx - (double)q.x, dy = (double)cy - (double)q.y;
+  if (dx * dx + dy * dy < p.cd2_thr) {          // sqrt(d2) < collision_dist (noVis_sim.py:81)
+    const int cell = cy * p.R + cx, sh = (cell & 15) * 2;
+    if ((sg[cell >> 4] >> sh) & 3u) {
+      const uint32_t code = (atomicAnd(sg + (cell >> 4), ~(3u << sh)) >> sh) & 3u;
+      if (code) {
+        atomicAnd(p.grid + (size_t)env * p.env_words + (cell >> 4), ~(3u << sh));   // write-through to HBM
+        atomicAdd(s_pk, (10 + (code == 2u ? 20 : 0)) | (1 << 16) | ((code == 2u ? 1 : 0) << 24));
+      }
+    }
+  }
+}
+
 // CTA-wide stage (4) from the shared-memory grid.
 template <typename OT>
-__device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint32_t* sg, int env, int tid, int nthr, OT* __restrict__ obs) {
+__device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint32_t* sg, int env, int tid, int nthr, OT* __restrict__ obs,
+                                                  const float2* sp = nullptr) {
   const ObsCvt<OT> cvt(p);
   if (p.obs_mode == 0) {
     const int RC = p.RC;
@@ -151,7 +196,7 @@ __device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint
     OT* o = obs + (size_t)env * p.D * WW;
     for (int it = tid; it < nitem; it += nthr) {
       const int i = it / W, b = it - i * W;
-      const float2 q = __ldcg(ps + i);
+      const float2 q = sp ? sp[i] : __ldcg(ps + i);
       const int cx = (int)floorf(q.x + 0.5f), gy = (int)floorf(q.y + 0.5f) - h + b;
       OT* dst = o + (size_t)i * WW + b * W;
       const bool row_ok = (unsigned)gy < (unsigned)p.C;
@@ -173,6 +218,8 @@ template <typename OT>
 __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io, int staged) {
   extern __shared__ __align__(128) unsigned char cta_smem[];
   __shared__ uint64_t bar;
+  __shared__ int s_pk;
+  __shared__ float2 s_pos[256];   // this step's positions of the env (wide path): spread test and window emission read them here
   uint32_t* const sg = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int flags = io.flags;
@@ -185,23 +232,43 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   __syncthreads();
   uint32_t phase = 0;
   StatAcc acc;
+  // production path: stages (1)-(2) on all threads, one drone per thread (30 * 255 < 2^16 keeps the packed totals exact)
+  const bool wide = staged && (flags & (F_MOVE | F_SCATTER | F_REWARD)) == (F_MOVE | F_SCATTER | F_REWARD) && p.cd_fast && !p.has_wait &&
+                    p.D <= 255 && p.D < (int)blockDim.x;
   for (int env = blockIdx.x; env < p.N; env += gridDim.x) {
-    if (staged) {
-      if (threadIdx.x == 0) {   // one TMA bulk copy: the env's whole packed grid
-        mbar_expect_tx(&bar, (uint32_t)p.env_words * 4u);
-        bulk_g2s(sg, p.grid + (size_t)env * p.env_words, (uint32_t)p.env_words * 4u, &bar);
-      }
-      mbar_wait(&bar, phase);
-      phase ^= 1u;
+    int4 m_pre = make_int4(0, 0, 0, 0);
+    if (staged && threadIdx.x == 0) {   // one TMA bulk copy: the env's whole packed grid
+      mbar_expect_tx(&bar, (uint32_t)p.env_words * 4u);
+      bulk_g2s(sg, p.grid + (size_t)env * p.env_words, (uint32_t)p.env_words * 4u, &bar);
+      if (wide) m_pre = __ldcg(p.meta + env);   // in flight together with the grid and the positions
     }
+    bool landed = !staged;
     for (int t = 0; t < io.T; ++t) {
-      if (stepping) {
-        if (warp == 0) step_env_warp(p, io, t, env, lane, acc, sg);
-        __syncthreads();   // warp 0's grid / position updates are visible to the CTA
+      if (stepping && wide) {
+        // stage (1) needs no grid: its loads overlap the bulk copy
+        const bool mine = (int)threadIdx.x < p.D;
+        float2 q = make_float2(0.f, 0.f);
+        if (threadIdx.x == 0) s_pk = 0;
+        if (mine) {
+          q = move_drone(p, io, t, env, threadIdx.x);
+          s_pos[threadIdx.x] = q;
+        }
+        if (!landed) { mbar_wait(&bar, phase); phase ^= 1u; landed = true; }
+        __syncthreads();   // s_pk is zero, the grid has landed
+        if (mine) scatter_drone(p, env, q, sg, &s_pk);
+        __syncthreads();   // clears (shared memory), positions (s_pos) and totals are visible to warp 0
+        if (warp == 0) step_env_warp(p, io, t, env, lane, acc, sg, &s_pk, s_pos, t == 0 ? &m_pre : nullptr);
+        __syncthreads();   // warp 0's grid / position updates (auto-reset) are visible to the CTA
+      } else {
+        if (!landed) { mbar_wait(&bar, phase); phase ^= 1u; landed = true; }
+        if (stepping) {
+          if (warp == 0) step_env_warp(p, io, t, env, lane, acc, sg);
+          __syncthreads();   // warp 0's grid / position updates are visible to the CTA
+        }
       }
       if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
         OT* o = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * p.N * p.obs_per_env);
-        if (staged) emit_obs_cta_smem<OT>(p, sg, env, threadIdx.x, blockDim.x, o);
+        if (staged) emit_obs_cta_smem<OT>(p, sg, env, threadIdx.x, blockDim.x, o, (stepping && wide) ? s_pos : nullptr);
         else emit_obs_global<OT>(p, env, threadIdx.x, blockDim.x, o);
         if (stepping && t + 1 < io.T) __syncthreads();   // emission reads precede the next step's clears
       }

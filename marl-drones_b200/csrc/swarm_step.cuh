@@ -90,7 +90,8 @@ __device__ __forceinline__ void reset_tile(const DevParams& p, int env, int epis
 // Rotation s pairs lane i with lane (i+s) mod D; s = 1..floor(D/2) covers every pair; exits as soon as every
 // tile that needs an answer has one (the first rotation almost always settles it).
 template <int TS>
-__device__ __forceinline__ bool tile_spread(const DevParams& p, int env, int tile, int tl, bool need, float x, float y) {
+__device__ __forceinline__ bool tile_spread(const DevParams& p, int env, int tile, int tl, bool need, float x, float y,
+                                            const float2* sp = nullptr) {   // sp: the env's positions in shared memory (D > 32 path), or null
   const int D = p.D;
   const double thr2 = p.spread2_thr;   // sqrt(d2) > row_count // n_drones  <=>  d2 > spread2_thr
   const unsigned tm = (TS == 32) ? FULL : (((1u << TS) - 1u) << (tile * TS));
@@ -115,7 +116,7 @@ __device__ __forceinline__ bool tile_spread(const DevParams& p, int env, int til
         for (int i = tl; i < D; i += TS) {
           int j = i + s;
           if (j >= D) j -= D;
-          const float2 a = __ldcg(ps + i), b = __ldcg(ps + j);
+          const float2 a = sp ? sp[i] : __ldcg(ps + i), b = sp ? sp[j] : __ldcg(ps + j);
           const double dx = (double)b.x - (double)a.x, dy = (double)b.y - (double)a.y;
           far = far || (dx * dx + dy * dy > thr2);
         }
