@@ -299,6 +299,10 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of replaying a CUDA graph of 32 steps")
     ap.add_argument("--clock-window-s", type=float, default=0.4, help="seconds of identical untimed steps run under the clock sampler right before the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stats-mode", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: how the per-step episode statistics cross GPUs — 'peer': pushed by the step kernel's last CTA into "
+                         "every rank's mailbox over NVLink peer memory (no collective kernel); 'nccl': swarm_stats_allreduce on a side stream")
+    ap.add_argument("--stats-every", type=int, default=1, help="N > 1: all-reduce the episode statistics every K steps (0 = never)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
@@ -335,11 +339,15 @@ def main():
     acts = torch.cat([half, (half + 2) % 4]).contiguous()
     n_act = acts.shape[0]
     stream = torch.cuda.current_stream(dev)
-    side = torch.cuda.Stream(dev) if world > 1 else None
+    side = torch.cuda.Stream(dev) if (world > 1 and args.stats_mode == "nccl") else None
     comm = None
-    if world > 1:
+    use_nccl = world > 1 and args.stats_mode == "nccl"
+    if use_nccl:
         from swarm_b200 import StatsComm
         comm = StatsComm()
+    elif world > 1:
+        for e in envs:
+            e.enable_peer_stats()
     snaps = [torch.zeros(8, dtype=torch.int64, device=dev) for _ in range(n_act)]
 
     def one_step(i, ev=None):
@@ -350,7 +358,7 @@ def main():
         envs[s].step(acts[i % n_act], out=obs[s])
         if ev is not None:
             ev[1].record(cur)
-        if world > 1:                       # the path's only collective: 64-byte episode statistics, off the critical path
+        if use_nccl and i % max(args.stats_every, 1) == 0:   # the path's only collective: 64-byte episode statistics
             snap = snaps[i % n_act]
             snap.copy_(envs[s].stats, non_blocking=True)
             side.wait_stream(cur)
@@ -491,6 +499,18 @@ def main():
     e8_value = float(n_envs) * D * E * world / (e8_ms * 1e-3)
     e8.close()
 
+    stats_global = None
+    if world > 1 and not use_nccl:          # what the mailboxes hold after the run: totals of ALL ranks for env batch 0
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        local = envs[0].stats.clone()
+        tot = local.clone()
+        dist.all_reduce(tot)                # checker only (outside every timed region): NCCL sum of the local totals
+        envs[0].push_stats()                # the in-step feed lags by one launch: publish the final totals explicitly
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        stats_global = envs[0].global_stats(min_pushes=1).tolist()
+        assert stats_global == tot.tolist(), (stats_global, tot.tolist())
     if rank == 0:
         peak, peak_src = load_peak()
         bytes_per_launch = algorithmic_bytes_per_env_step(kw) * n_envs
@@ -503,7 +523,9 @@ def main():
                        "obs_dtype": "float32", "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
                        "actions": "uint8 uniform{0..3} (16 draws + their opposites, zero net drift), pre-generated on device",
                        "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * 4 + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
-                       "parallelism": f"env-sharded x{world}, no data-path collective; 64 B stats all-reduce on a side stream"},
+                       "parallelism": f"env-sharded x{world}, no data-path collective; per-step episode statistics: " +
+                                      ("published by the step kernel into every rank's mailbox over NVLink peer memory (posted stores at kernel start, no collective kernel)"
+                                       if not use_nccl else f"swarm_stats_allreduce (NCCL) on a side stream every {max(args.stats_every, 1)} step(s)")},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": load_traffic(args.workload), "peak_source": peak_src, "kernel": "swarm::step_warp_kernel (swarm::step_cta_kernel for cfg5a/cfg5b)",
                          "kernel_ms_avg": kern_avg_ms, "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
@@ -514,6 +536,7 @@ def main():
                     "steps": E, "ms_per_step": e2e_ms / E, "api": "swarm_step_host (pinned host buffers, full obs D2H)"},
             "e2e_uint8_obs": {"value": e8_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                               "d2h_bytes_per_step": int(obs8_h.numel() + n_envs * 4 + n_envs + 64), "steps": E, "ms_per_step": e8_ms / E},
+            "stats_global_env_batch0": stats_global,
             "gpu_launches": launches, "clocks": dict(clocks, window=f"{hold} untimed steps + the {K} timed steps, continuous load"),
         }
         if world == 1 and not args.no_cpu_baseline:

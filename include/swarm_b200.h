@@ -200,6 +200,23 @@ int swarm_comm_destroy(void* comm);
  * swarm_step_host), enqueued on `stream`; integer sums, so the result does not depend on the reduction order. */
 int swarm_stats_allreduce(SwarmEnv* env, int64_t* stats, void* comm, void* stream);
 
+/* Fused form of the same exchange over NVLink peer memory (no collective kernel, no extra launch): every rank owns a
+ * small mailbox; once the mailboxes are exchanged, every swarm_step / swarm_rollout launch that is given a statistics
+ * buffer publishes, as its FIRST action (one thread, 16-byte posted stores, nothing waits on them), the buffer's running
+ * totals as the previous launches left them into this rank's slot of every rank's mailbox — the feed lags the step by one
+ * launch and costs it nothing.  swarm_stats_push publishes the current totals explicitly (stream-ordered, exact).
+ * Ranks = processes of ONE node, world <= 8.
+ *   swarm_stats_mailbox_handle  allocates the mailbox on first use, returns its cudaIpcMemHandle_t (64 bytes)
+ *   swarm_stats_peers_open      handles = [world][64] gathered from all ranks (own entry ignored); enables the pushes
+ *   swarm_stats_push            one-thread kernel: publish stats_dev (NULL = the handle's internal statistics) now
+ *   swarm_stats_global          out_dev int64[8] (device) = sum over ranks of their latest complete totals; waits (bounded)
+ *                               until every rank has pushed at least min_pushes times (0 = whatever has arrived)        */
+int swarm_stats_mailbox_handle(SwarmEnv* env, uint8_t* handle_out_64);
+int swarm_stats_peers_open(SwarmEnv* env, const uint8_t* handles, int32_t rank, int32_t world);
+int swarm_stats_peers_close(SwarmEnv* env);
+int swarm_stats_push(SwarmEnv* env, const int64_t* stats_dev, void* stream);
+int swarm_stats_global(SwarmEnv* env, int64_t min_pushes, int64_t* out_dev, void* stream);
+
 /* -- diagnostics ---------------------------------------------------------------------------- */
 /* Synchronises `stream`, reads the sticky device error word; clears it when clear != 0. */
 int swarm_device_error(SwarmEnv* env, int32_t* code_out, int clear, void* stream);

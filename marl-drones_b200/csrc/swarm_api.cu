@@ -29,6 +29,10 @@ struct SwarmEnv {
   float* h_rew_dev;
   uint8_t* h_done_dev;
   int* cover_dev;
+  // peer-memory statistics exchange
+  unsigned long long* mbox;          // this rank's mailbox, int64 [SWARM_MAX_RANKS][SWARM_MBOX_SLOT]
+  unsigned long long* gstats_dev;    // int64[8] scratch for swarm_stats_global with a host destination
+  void* peer_open[SWARM_MAX_RANKS];  // mappings returned by cudaIpcOpenMemHandle (null for this rank / unused)
 };
 
 static thread_local char g_cuda_err[256] = "";
@@ -238,6 +242,9 @@ extern "C" int swarm_destroy(SwarmEnv* e) {
   cudaFree(e->p.grid); cudaFree(e->p.pos); cudaFree(e->p.meta); cudaFree(e->p.wait); cudaFree(e->p.err);
   cudaFree(e->stats_dev); cudaFree(e->cover_dev);
   cudaFree(e->h_act_dev); cudaFree(e->h_obs_dev); cudaFree(e->h_rew_dev); cudaFree(e->h_done_dev);
+  for (int r = 0; r < SWARM_MAX_RANKS; ++r)
+    if (e->peer_open[r]) cudaIpcCloseMemHandle(e->peer_open[r]);
+  cudaFree(e->mbox); cudaFree(e->p.peers.pushes); cudaFree(e->gstats_dev);
   delete e;
   return SWARM_OK;
 }
@@ -405,7 +412,7 @@ extern "C" int swarm_step(SwarmEnv* e, const void* actions, int action_dtype, vo
   if (!e || !actions || !reward_out || !done_out || action_dtype < 0 || action_dtype > 2) return SWARM_ERR_INVALID_ARG;
   int rc = use_device(e);
   if (rc) return rc;
-  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
+  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0) | F_PUSH);
   io.actions = actions; io.act_dtype = action_dtype; io.obs_out = obs_out;
   io.reward_out = reward_out; io.done_out = done_out; io.stats = (unsigned long long*)stats_accum;
   return launch_step(e, io, (cudaStream_t)stream);
@@ -416,7 +423,7 @@ extern "C" int swarm_rollout(SwarmEnv* e, int32_t T, const uint8_t* actions, voi
   if (!e || T < 1 || !actions || !reward_out || !done_out) return SWARM_ERR_INVALID_ARG;
   int rc = use_device(e);
   if (rc) return rc;
-  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
+  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0) | F_PUSH);
   io.T = T;
   io.actions = actions; io.act_dtype = SWARM_ACT_U8; io.obs_out = obs_out; io.obs_last_only = obs_last_only ? 1 : 0;
   io.reward_out = reward_out; io.done_out = done_out; io.stats = (unsigned long long*)stats_accum;
@@ -639,4 +646,85 @@ extern "C" int swarm_stats_allreduce(SwarmEnv* e, int64_t* stats, void* comm, vo
   void* buf = stats ? (void*)stats : (void*)e->stats_dev;
   int n = g_nccl.AllReduce(buf, buf, SWARM_STAT_COUNT, kNcclInt64, kNcclSum, comm, (cudaStream_t)stream);
   return n ? nccl_fail("ncclAllReduce", n) : SWARM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ peer-memory statistics
+// The fused form of the path's one collective: no NCCL kernel, no extra launch — the step kernel publishes this rank's running
+// totals into every rank's mailbox over NVLink at its start (peer_stats_push, swarm_common.cuh).
+static int ensure_mailbox(SwarmEnv* e) {
+  if (e->mbox) return SWARM_OK;
+  const size_t bytes = (size_t)SWARM_MAX_RANKS * SWARM_MBOX_SLOT * sizeof(unsigned long long);
+  CUDA_TRY(cudaMalloc((void**)&e->mbox, bytes));
+  CUDA_TRY(cudaMemset(e->mbox, 0, bytes));
+  CUDA_TRY(cudaMalloc((void**)&e->p.peers.pushes, 16));
+  CUDA_TRY(cudaMemset(e->p.peers.pushes, 0, 16));
+  CUDA_TRY(cudaMalloc((void**)&e->gstats_dev, 64));
+  return SWARM_OK;
+}
+
+extern "C" int swarm_stats_mailbox_handle(SwarmEnv* e, uint8_t* handle_out) {
+  if (!e || !handle_out) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  if ((rc = ensure_mailbox(e))) return rc;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  cudaIpcMemHandle_t h;
+  CUDA_TRY(cudaIpcGetMemHandle(&h, e->mbox));
+  memcpy(handle_out, &h, 64);
+  return SWARM_OK;
+}
+
+extern "C" int swarm_stats_peers_open(SwarmEnv* e, const uint8_t* handles, int32_t rank, int32_t world) {
+  if (!e || !handles || world < 1 || world > SWARM_MAX_RANKS || rank < 0 || rank >= world) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  if ((rc = ensure_mailbox(e))) return rc;
+  if (e->p.peers.n_ranks > 0) return SWARM_ERR_INVALID_ARG;   // already open
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) { e->p.peers.mbox[r] = e->mbox; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handles + (size_t)r * 64, 64);
+    void* ptr = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    e->peer_open[r] = ptr;
+    e->p.peers.mbox[r] = (unsigned long long*)ptr;
+  }
+  e->p.peers.rank = rank;
+  e->p.peers.n_ranks = world;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_stats_peers_close(SwarmEnv* e) {
+  if (!e) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  CUDA_TRY(cudaDeviceSynchronize());
+  e->p.peers.n_ranks = 0;
+  for (int r = 0; r < SWARM_MAX_RANKS; ++r) {
+    if (e->peer_open[r]) CUDA_TRY(cudaIpcCloseMemHandle(e->peer_open[r]));
+    e->peer_open[r] = nullptr;
+    e->p.peers.mbox[r] = nullptr;
+  }
+  return SWARM_OK;
+}
+
+extern "C" int swarm_stats_push(SwarmEnv* e, const int64_t* stats_dev, void* stream) {
+  if (!e || e->p.peers.n_ranks < 1) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  peer_stats_push_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->p.peers, stats_dev ? (const unsigned long long*)stats_dev : e->stats_dev);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_stats_global(SwarmEnv* e, int64_t min_pushes, int64_t* out_dev, void* stream) {
+  if (!e || !out_dev || min_pushes < 0 || e->p.peers.n_ranks < 1) return SWARM_ERR_INVALID_ARG;
+  int rc = use_device(e);
+  if (rc) return rc;
+  peer_stats_reduce_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(e->mbox, e->p.peers.n_ranks, (unsigned long long)min_pushes,
+                                                                (unsigned long long*)out_dev);
+  e->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
 }

@@ -18,6 +18,19 @@ constexpr unsigned FULL = 0xffffffffu;
 
 enum : int { F_MOVE = 1, F_SCATTER = 2, F_REWARD = 4, F_OBS = 8, F_ALL = 15 };
 
+// Peer-memory statistics exchange (SURVEY §8e "fused one-shot variant"): every rank owns a mailbox of SWARM_MAX_RANKS slots,
+// slot r = eight {value, version} pairs written by rank r with 16-byte stores over NVLink (peer-mapped through CUDA IPC).
+// The push rides at the START of a step launch (CTA 0, thread 0): it publishes the running totals as they stand after the
+// PREVIOUS launch — final by stream order — so it overlaps the whole kernel and costs the step nothing; the stores are
+// posted (no fence, no read over NVLink).  swarm_stats_push publishes the current totals explicitly when exactness matters.
+constexpr int SWARM_MAX_RANKS = 8;
+constexpr int SWARM_MBOX_SLOT = 16;   // int64 words per slot: 8 x {value, version}
+struct PeerStats {
+  unsigned long long* mbox[SWARM_MAX_RANKS];   // mailbox base of every rank (own one included), null beyond n_ranks
+  unsigned long long* pushes;                  // number of pushes this rank has made (device counter, = the version)
+  int n_ranks, rank;                           // n_ranks == 0: exchange disabled
+};
+
 struct DevParams {
   // configuration (mirrors DroneEnv.__init__, A2C/noVis_sim.py:8-17)
   int N, D, R, C, RC, U, n_anom;
@@ -44,6 +57,7 @@ struct DevParams {
   uint32_t seed_lo, seed_hi;
   long long env_id_base;
   // resident state
+  PeerStats peers;
   uint32_t* grid;
   float2* pos;
   int4* meta;
@@ -139,6 +153,48 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
 __device__ __forceinline__ uint4 draw_block(const DevParams& p, long long env_id, uint32_t episode, uint32_t block) {
   return philox4x32_10(make_uint4((uint32_t)(unsigned long long)env_id, (uint32_t)((unsigned long long)env_id >> 32), episode, block),
                        p.seed_lo, p.seed_hi);
+}
+
+// One thread: publish stats[0..8) (read from L2, where the previous launch's atomics left them) to every rank's mailbox.
+__device__ __forceinline__ void peer_stats_push(const PeerStats& ps, const unsigned long long* stats) {
+  const unsigned long long ver = *ps.pushes + 1ull;      // only this thread of this launch touches the counter
+  *ps.pushes = ver;
+  unsigned long long v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = __ldcg(stats + k);
+  for (int r = 0; r < ps.n_ranks; ++r) {
+    ulonglong2* slot = reinterpret_cast<ulonglong2*>(ps.mbox[r] + (size_t)ps.rank * SWARM_MBOX_SLOT);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) __stcg(slot + k, make_ulonglong2(v[k], ver));   // 16-byte posted stores
+  }
+}
+__global__ void peer_stats_push_kernel(PeerStats ps, const unsigned long long* stats) { peer_stats_push(ps, stats); }
+
+// Sums the latest complete totals of all ranks' slots of THIS rank's mailbox into out[8]; waits (bounded) until every slot has
+// been pushed at least min_push times.  One thread per rank slot; a slot is complete when its eight versions agree.
+__global__ void peer_stats_reduce_kernel(const unsigned long long* mbox, int n_ranks, unsigned long long min_push, unsigned long long* out) {
+  __shared__ unsigned long long acc[8];
+  if (threadIdx.x < 8) acc[threadIdx.x] = 0ull;
+  __syncthreads();
+  if ((int)threadIdx.x < n_ranks) {
+    const volatile unsigned long long* slot = mbox + (size_t)threadIdx.x * SWARM_MBOX_SLOT;
+    unsigned long long v[8];
+    for (long long spin = 0; spin < (1ll << 24); ++spin) {
+      const unsigned long long ver = slot[1];
+      bool ok = ver >= min_push;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        v[k] = slot[2 * k];
+        ok = ok && slot[2 * k + 1] == ver;
+      }
+      if (ok && slot[1] == ver) break;
+      __nanosleep(200);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) atomicAdd(&acc[k], v[k]);
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) out[threadIdx.x] = acc[threadIdx.x];
 }
 
 // per-thread statistics accumulator; reduced once per CTA, 6 atomics per CTA

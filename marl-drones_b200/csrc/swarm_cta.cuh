@@ -225,6 +225,8 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   const int flags = io.flags;
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
   const bool stepping = (flags & (F_MOVE | F_SCATTER | F_REWARD)) != 0;
+  if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0 && threadIdx.x == 0)
+    peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
   if (staged && threadIdx.x == 0) {
     mbar_init(&bar, 1);
     fence_mbar_init();

@@ -16,6 +16,8 @@
 namespace swarm {
 
 constexpr int F_RESET = 16;   // auto-reset on done inside the step (A2C/envs.py:22-26)
+constexpr int F_PUSH = 32;    // publish the running statistics to the ranks' mailboxes (swarm_step / swarm_rollout only: their
+                              // statistics buffer holds running totals; swarm_step_host's is zeroed per call)
 
 struct StepIO {
   const void* actions;     // [T][N][D] of act_dtype

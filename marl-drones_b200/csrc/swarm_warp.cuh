@@ -184,6 +184,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   const bool has_wait = FAST ? false : (p.has_wait != 0);
   const bool want_stats = LEAN ? true : (io.stats != nullptr && (flags & F_REWARD));
   const ObsCvt<OT> cvt(p);
+  if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0 && threadIdx.x == 0)
+    peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
   if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
   if constexpr (MODE == 1 && sizeof(OT) == 4) {
     for (int b = threadIdx.x; b < 256; b += blockDim.x) lut4[b] = make_float4(cvt.sel(b, 0), cvt.sel(b, 1), cvt.sel(b, 2), cvt.sel(b, 3));

@@ -212,6 +212,41 @@ class BatchedDroneEnv:
     def stats_dict(self):
         return dict(zip(STAT_NAMES, self.stats.tolist()))
 
+    # -------------------------------------------------------------------------------------- peer-memory statistics
+    def enable_peer_stats(self, group=None):
+        """Multi-GPU (one process per GPU of one node): exchange the ranks' mailbox handles through torch.distributed once;
+        from then on every step launch publishes this rank's running statistics into every rank's mailbox over NVLink
+        (swarm_stats_peers_open; no collective on the step path).  With no process group it is a world of one."""
+        import torch.distributed as dist
+        on = dist.is_available() and dist.is_initialized()
+        rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
+        h = (C.c_uint8 * 64)()
+        check(self._L.swarm_stats_mailbox_handle(self._h, h))
+        handles = [bytes(h)]
+        if world > 1:
+            handles = [None] * world
+            dist.all_gather_object(handles, bytes(h), group=group)
+        buf = (C.c_uint8 * (64 * world)).from_buffer_copy(b"".join(handles))
+        check(self._L.swarm_stats_peers_open(self._h, buf, rank, world))
+        self._peer_world = world
+        self._gstats = torch.zeros(8, dtype=torch.int64, device=self.device)
+        return self
+
+    def push_stats(self):
+        """Publish the CURRENT running totals to every rank's mailbox (stream-ordered after the steps enqueued so far)."""
+        check(self._L.swarm_stats_push(self._h, self._stats_ptr, self._stream()))
+
+    def global_stats(self, min_pushes=0, out=None):
+        """int64[8] (device): the sum over all ranks of their latest pushed running totals (waits until every rank has pushed
+        at least `min_pushes` times).  Every step launch of a rank publishes, at its start, the totals as the previous launch
+        left them (the feed lags by one step and costs the step nothing); `push_stats()` publishes the current totals."""
+        out = self._gstats if out is None else out
+        check(self._L.swarm_stats_global(self._h, int(min_pushes), self._ptr(out), self._stream()))
+        return out
+
+    def disable_peer_stats(self):
+        check(self._L.swarm_stats_peers_close(self._h))
+
     def allreduce_stats(self, group=None):
         """The only collective on this path: ncclAllReduce(SUM, int64[8]) of the episode statistics (64 B per rank)."""
         from .sharding import reduce_stats
