@@ -167,6 +167,27 @@ def run_reference(args, kw, n_envs, rank, world):
     }))
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner) print to fd 1; the contract is ONE JSON line on stdout.  Everything written to fd 1
+    from here on goes to stderr; emit() writes the JSON line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def run_a2c(args, rank, world, local):
     """BASELINE configs[3] / SURVEY §8f-1: the batched re-expression of A2C/train.py::train() — per outer iteration T =
     --rollout-steps times (16 stacked MlpPolicy nets forward with autograd -> swarm_sample_actions -> fused env step), then the
@@ -182,6 +203,7 @@ def run_a2c(args, rank, world, local):
                               "unavailable": "the reference train() is pure Python/PyTorch under /root/reference and cannot travel to the GPU box; "
                                              "measured in the build container: 47.2 agent-steps/s (8 cores, 10x10, 8 drones, MLP; BASELINE.md)"}))
         return
+    quiet_stdout()
     import torch
     import torch.distributed as dist
     from swarm_b200 import BatchedDroneEnv
@@ -273,7 +295,7 @@ def run_a2c(args, rank, world, local):
             "clocks": clocks,
             "cpu_baseline": {"value": 47.2, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified A2C/train.py::train(), 250 env-steps, 10x10, 8 drones, MLP, measured in the build container (cannot travel to the GPU box)"},
         }
-        print(json.dumps(line))
+        emit(line)
     sys.stdout.flush()
     torch.cuda.synchronize(dev)
     if world > 1:
@@ -317,6 +339,7 @@ def main():
     if args.impl == "reference":
         return run_reference(args, kw, n_envs, rank, world)
 
+    quiet_stdout()
     import torch
     import torch.distributed as dist
     from swarm_b200 import BatchedDroneEnv
@@ -544,7 +567,7 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
             v2, _, sample2, _ = cpu_port_throughput(kw, budget_s=4.0, scan_mode=1)
             line["cpu_baseline_windowed"] = {"value": v2, "unit": UNIT, "cores": cores, "kind": "port (ours: bounded-window scan, not the reference's algorithm)", "sample": sample2}
-        print(json.dumps(line))
+        emit(line)
     sys.stdout.flush()
     # teardown: release the captured graph (it holds NCCL work) before the communicator, and leave without running the
     # interpreter's module teardown, which can dead-lock on a communicator that was used under graph capture
