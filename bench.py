@@ -362,15 +362,30 @@ def main():
     acts = torch.cat([half, (half + 2) % 4]).contiguous()
     n_act = acts.shape[0]
     stream = torch.cuda.current_stream(dev)
-    side = torch.cuda.Stream(dev) if (world > 1 and args.stats_mode == "nccl") else None
     comm = None
     use_nccl = world > 1 and args.stats_mode == "nccl"
+    if world > 1 and not use_nccl:
+        ok = 1
+        try:
+            for e in envs:
+                e.enable_peer_stats()
+        except Exception as exc:            # CUDA IPC unavailable between these processes: every rank switches to the NCCL form
+            print(f"[bench] rank {rank}: peer-memory statistics unavailable ({exc!r}); using --stats-mode nccl", file=sys.stderr)
+            ok = 0
+        flag = torch.tensor([ok], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            use_nccl = True
+            for e in envs:
+                try:
+                    e.disable_peer_stats()
+                except Exception:
+                    pass
+    side = None
     if use_nccl:
         from swarm_b200 import StatsComm
         comm = StatsComm()
-    elif world > 1:
-        for e in envs:
-            e.enable_peer_stats()
+        side = torch.cuda.Stream(dev)       # the all-reduce runs beside the step stream
     snaps = [torch.zeros(8, dtype=torch.int64, device=dev) for _ in range(n_act)]
 
     def one_step(i, ev=None):

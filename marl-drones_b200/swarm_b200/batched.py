@@ -221,11 +221,15 @@ class BatchedDroneEnv:
         on = dist.is_available() and dist.is_initialized()
         rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
         h = (C.c_uint8 * 64)()
-        check(self._L.swarm_stats_mailbox_handle(self._h, h))
-        handles = [bytes(h)]
+        rc = self._L.swarm_stats_mailbox_handle(self._h, h)
+        mine = bytes(h) if rc == 0 else None       # a rank that cannot export still takes part in the gather (no deadlock)
+        handles = [mine]
         if world > 1:
             handles = [None] * world
-            dist.all_gather_object(handles, bytes(h), group=group)
+            dist.all_gather_object(handles, mine, group=group)
+        if any(x is None for x in handles):
+            check(rc)
+            raise SwarmError("another rank could not export its statistics mailbox (CUDA IPC)")
         buf = (C.c_uint8 * (64 * world)).from_buffer_copy(b"".join(handles))
         check(self._L.swarm_stats_peers_open(self._h, buf, rank, world))
         self._peer_world = world
