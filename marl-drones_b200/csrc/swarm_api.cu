@@ -191,6 +191,10 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
       if (warps > 32) warps = 32;
       if (warps > best) { best = (int)warps; e->wpb = w; }
     }
+    if (const char* v = getenv("SWARM_WPB")) {   // tuning knob: force the CTA size (2, 4 or 8 warps)
+      const int w = atoi(v);
+      if (w == 2 || w == 4 || w == 8) e->wpb = w;
+    }
     if (e->staged) {   // CTA-level input buffer for EPC = wpb * EPW envs
       const long long epc = (long long)e->wpb * (32 / e->ts);
       const int gridb = (int)(epc * p.env_words * 4), posb = align16(epc * c->n_drones * 8), metab = (int)(epc * 16);
