@@ -19,11 +19,23 @@
 #include "swarm_emit.cuh"
 #include "swarm_step.cuh"
 
+#ifndef SWARM_TRACE
+#define SWARM_TRACE 0   // 1: instrumented build for tools/trace.py (per-CTA start / end / SM id / input-wait cycles, CTA 0 timeline)
+#endif
 #ifndef SWARM_MINB
 #define SWARM_MINB 3   // resident CTAs per SM the staged kernel is compiled for (register cap 65536 / (256 * SWARM_MINB))
 #endif
 
 namespace swarm {
+
+#if SWARM_TRACE
+__device__ unsigned long long g_trace[16 * 8 * 8];   // CTA 0: clock64 at events 0..6 of its first 16 iterations, per warp
+__device__ unsigned long long g_cta_t[2048 * 2];     // [2b], [2b+1]: globaltimer at CTA b's start / end; [2048+b] wait cycles; [3072+b] SM id
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TR(ev) do { if (blockIdx.x == 0 && lane == 0 && it < 16) g_trace[(it * 8 + wib) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define TR(ev) do { } while (0)
+#endif
 
 // init_env (A2C/noVis_sim.py:36-63) for the env of this tile, built in shared memory and copied out to HBM.
 // Same RNG spec as reset_tile / oracle_reset_env.  Called by all 32 lanes; `doit` is tile-uniform; q = the lane's new position.
@@ -242,6 +254,9 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     }
   };
 
+#if SWARM_TRACE
+  if (threadIdx.x == 0) { unsigned sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); g_cta_t[blockIdx.x * 2] = gtimer(); g_cta_t[2048 + blockIdx.x] = 0; g_cta_t[1024 * 3 + blockIdx.x] = sm; }
+#endif
   uint32_t phases = 0;
   const bool producer = threadIdx.x == 0;
   if (producer && (int)blockIdx.x < ncg) produce(blockIdx.x, 0);
@@ -250,10 +265,12 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     const int b = it & 1;
     // refill the other buffer for the CTA's next iteration as soon as every warp has released it (it was read in iteration
     // it-1; its (it-1)/2-th release completes phase ((it-1)/2) & 1 of empty_bar[b^1])
+    TR(0);
     if (producer && cg + (int)gridDim.x < ncg) {
       if (it >= 1) mbar_wait_s(empty_s + 8u * (uint32_t)(b ^ 1), (uint32_t)((it - 1) >> 1) & 1u);
       produce(cg + gridDim.x, b ^ 1);
     }
+    TR(1);
     const int grp = cg * wpb + wib;
     if (!LEAN && grp >= ngroups) continue;   // idle warp of the tail CTA-group (last iteration only)
     unsigned char* const in = inbuf0 + b * p.in_bytes;
@@ -277,8 +294,16 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     if (active && !pos_tma) q = __ldcg(pp);
     if (active && !act_tma && (flags & F_MOVE)) a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
 
+    TR(2);
+#if SWARM_TRACE
+    const long long tw0 = clock64();
+#endif
     mbar_wait_s(full_s + 8u * (uint32_t)b, (phases >> b) & 1u);
     phases ^= 1u << b;
+#if SWARM_TRACE
+    if (threadIdx.x == 32) g_cta_t[2048 + blockIdx.x] += (unsigned long long)(clock64() - tw0);   // warp 1: cycles waiting for input
+#endif
+    TR(3);
     if (active && pos_tma) q = reinterpret_cast<const float2*>(in + p.off_pos)[(wib * EPW + tile) * D + tl];
     if (active && act_tma) a = (int)in[p.off_act + (wib * EPW + tile) * D + tl];
     if (valid && tl == 0 && meta_tma) m = reinterpret_cast<const int4*>(in + p.off_meta)[wib * EPW + tile];
@@ -312,8 +337,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
           }
           // drones of one env on one cell form a match group; its lowest lane resolves the conflict for all of them.
           // (Measured: guarding the match with "does any lane stand on an unmapped cell", or electing the winner by the return
-          // value of a shared-memory atomicAnd instead, both make the cfg3 step 50 % SLOWER — DESIGN.md §5 — so the match is
-          // unconditional.)
+          // value of a shared-memory atomicAnd instead, both make the cfg3 step SLOWER — the warps then run in closer lock
+          // step and a random ~10 % of the CTAs is starved of TMA input, DESIGN.md §5 — so the match is unconditional.)
           const unsigned key = cand ? (((unsigned)tile << 24) | (unsigned)cell) : (0x80000000u | (unsigned)lane);
           const unsigned mm = __match_any_sync(FULL, key);
           if (cand && lane == __ffs(mm) - 1) {
@@ -408,6 +433,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
         if (MODE == 0) {
           emit_full_smem<OT>(p, cvt, sgrid, nenv, lane, obase + (size_t)env0 * p.RC);
         } else {
+          TR(4);
           if (lane == 0) bulk_wait_read0();   // the previous bulk store has drained `stage` (long ago)
           __syncwarp();
           if (active) build_window<WC, OT>(p, cvt, lut4, sg, q, my_stage);
@@ -430,9 +456,14 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
     }
     fence_proxy_async();   // this group's generic accesses to the input buffer precede the bulk copy that refills it
     __syncwarp();
+    TR(5);
     if (lane == 0) mbar_arrive_s(empty_s + 8u * (uint32_t)b);   // release the buffer to the producer
+    TR(6);
   }
   if (lane == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
+#if SWARM_TRACE
+  if (threadIdx.x == 0) g_cta_t[blockIdx.x * 2 + 1] = gtimer();
+#endif
 
   if (want_stats) {   // one lane per warp adds the warp's (uniform) totals; zero entries are skipped
     if (lane == 0) {

@@ -27,3 +27,7 @@ timeit(lambda i: envs[i % sets].stage_obs(out=obs[i % sets]), "obs only (generic
 timeit(lambda i: envs[i % sets].stage_move(acts[i % 8]), "move only")
 timeit(lambda i: obs[i % sets].zero_(), "torch zero_ of obs")
 timeit(lambda i: obs[i % sets].copy_(obs[(i + 1) % sets]), "torch copy_ obs->obs")
+# the same step with uint8 observations (26 MB instead of 105 MB of obs per cfg3 step): how much of the step is obs bandwidth
+envs8 = [BatchedDroneEnv(n, auto_reset=True, seed=1, env_id_base=s * n, obs_dtype=torch.uint8, **kw) for s in range(sets)]
+obs8 = [torch.empty(e.obs_shape, dtype=torch.uint8, device="cuda") for e in envs8]
+timeit(lambda i: envs8[i % sets].step(acts[i % 8], out=obs8[i % sets]), "step, uint8 obs")
