@@ -314,6 +314,8 @@ def main():
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + [A2C_WORKLOAD])
     ap.add_argument("--rollout-steps", type=int, default=25, help="cfg4_a2c: env steps per outer iteration (A2C/main.py default)")
     ap.add_argument("--tf32", action="store_true", help="cfg4_a2c: allow TF32 tensor-core GEMMs for the policy (default: fp32, as the reference)")
+    ap.add_argument("--obs-dtype", default="float32", choices=["float32", "uint8"],
+                    help="observation element type of the device-timed step (default float32 = the reference's; uint8 is a diagnostic line)")
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
@@ -352,9 +354,11 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     D = kw["n_drones"]
     K, W = args.steps, max(args.warmup, 3)
-    envs = [BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=(rank * args.sets + s) * n_envs, **kw)
+    obs_dt = torch.float32 if args.obs_dtype == "float32" else torch.uint8
+    s_o = 4 if args.obs_dtype == "float32" else 1
+    envs = [BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=(rank * args.sets + s) * n_envs, obs_dtype=obs_dt, **kw)
             for s in range(args.sets)]
-    obs = [torch.empty(e.obs_shape, dtype=torch.float32, device=dev) for e in envs]
+    obs = [torch.empty(e.obs_shape, dtype=obs_dt, device=dev) for e in envs]
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     # 32 pre-generated action tensors: 16 i.i.d. uniform draws followed by their opposites ((a+2) mod 4), so a cycle has no
     # net drift and the drones keep wandering instead of piling up against a wall over thousands of steps.
@@ -495,7 +499,7 @@ def main():
     # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region)
     e0 = envs[0]
     a_h = torch.empty((n_act, n_envs, D), dtype=torch.uint8).pin_memory(); a_h.copy_(acts.cpu())
-    obs_h = torch.empty(e0.obs_shape, dtype=torch.float32).pin_memory()
+    obs_h = torch.empty(e0.obs_shape, dtype=obs_dt).pin_memory()
     rew_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
     done_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
     stats_h = torch.zeros(8, dtype=torch.int64).pin_memory()
@@ -515,7 +519,7 @@ def main():
         e2e_ms = float(t.item())
     e2e_value = float(n_envs) * D * E * world / (e2e_ms * 1e-3)
     h2d = n_envs * D
-    d2h = int(obs_h.numel() * 4 + n_envs * 4 + n_envs + 64)
+    d2h = int(obs_h.numel() * s_o + n_envs * 4 + n_envs + 64)
     # the same host-buffer call with uint8 observations (values 0 / 1 / U, pad 255): the reference's obs are small integers
     # (int64 on the host, A2C/noVis_sim.py:168-170) that callers cast to float32 themselves, so a byte per cell loses nothing
     # and quarters the PCIe traffic that bounds e2e.  Reported beside, not instead of, the float32 number.
@@ -551,25 +555,25 @@ def main():
         assert stats_global == tot.tolist(), (stats_global, tot.tolist())
     if rank == 0:
         peak, peak_src = load_peak()
-        bytes_per_launch = algorithmic_bytes_per_env_step(kw) * n_envs
+        bytes_per_launch = algorithmic_bytes_per_env_step(kw, s_o=s_o) * n_envs
         achieved = bytes_per_launch / (kern_avg_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "u2 grid codes / f32 positions+obs (integer rewards)", "data": "synthetic",
             "config": {"workload": args.workload, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw,
-                       "obs_dtype": "float32", "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
+                       "obs_dtype": args.obs_dtype, "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
                        "actions": "uint8 uniform{0..3} (16 draws + their opposites, zero net drift), pre-generated on device",
-                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * 4 + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
+                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * s_o + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
                        "parallelism": f"env-sharded x{world}, no data-path collective; per-step episode statistics: " +
                                       ("published by the step kernel into every rank's mailbox over NVLink peer memory (posted stores at kernel start, no collective kernel)"
                                        if not use_nccl else f"swarm_stats_allreduce (NCCL) on a side stream every {max(args.stats_every, 1)} step(s)")},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": load_traffic(args.workload), "peak_source": peak_src, "kernel": "swarm::step_warp_kernel (swarm::step_cta_kernel for cfg5a/cfg5b)",
+                         "traffic": load_traffic(args.workload) if args.obs_dtype == "float32" else None, "peak_source": peak_src, "kernel": "swarm::step_warp_kernel (swarm::step_cta_kernel for cfg5a/cfg5b)",
                          "kernel_ms_avg": kern_avg_ms, "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
                          "launch": "CUDA graph of 32 steps" if graph is not None else "eager",
                          "algorithmic_bytes_per_launch": bytes_per_launch,
-                         "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw) / D},
+                         "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw, s_o=s_o) / D},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": E, "ms_per_step": e2e_ms / E, "api": "swarm_step_host (pinned host buffers, full obs D2H)"},
             "e2e_uint8_obs": {"value": e8_value, "unit": UNIT, "h2d_bytes_per_step": h2d,

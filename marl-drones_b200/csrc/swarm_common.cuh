@@ -127,6 +127,20 @@ __device__ __forceinline__ void mbar_arrive_s(uint32_t bar_s) {
 __device__ __forceinline__ void bulk_s2g_s(void* dst_gmem, uint32_t src_s, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(src_s), "r"(bytes) : "memory");
 }
+// the same copies with an L2 eviction-priority policy (createpolicy)
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_s2g_s_hint(void* dst_gmem, uint32_t src_s, uint32_t bytes, uint64_t pol) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst_gmem), "r"(src_s), "r"(bytes), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_s_hint(uint32_t dst_s, const void* src_gmem, uint32_t bytes, uint32_t bar_s, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst_s),
+               "l"(src_gmem), "r"(bytes), "r"(bar_s), "l"(pol)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
