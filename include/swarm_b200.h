@@ -188,6 +188,18 @@ int swarm_nstep_returns(const float* rewards, const uint8_t* dones, const float*
                         int64_t n_envs, int32_t n_drones, float gamma, float* returns_out,
                         float* coef_out, void* stream);
 
+/* The GRU cell of the stacked policy nets (A2C/models.py:104, `_, h = self.gru(x.unsqueeze(0))`: ONE step from h0 = 0, so
+ * only bias_hh survives of the hidden side), after the input-side GEMM, fused into one pass:
+ *   r = sigmoid(gi_r + bh_r), z = sigmoid(gi_z + bh_z), n = tanh(gi_n + r * bh_n), h = (1 - z) * n   (gate order r, z, n)
+ * gi float32 [N][G][3H] (= x W_ih^T + b_ih), bias_hh float32 [G][3H] -> h_out float32 [G][N][H].  G = 2D stacked nets. */
+int swarm_gru_gates_fwd(const float* gi, const float* bias_hh, int64_t n_envs, int32_t n_nets,
+                        int32_t hidden, float* h_out, void* stream);
+/* Its backward: dh float32 [G][N][H] -> dgi_out float32 [N][G][3H] (gradient of the pre-activations = of gi; summed over N
+ * it is also the gradient of b_ih and of the r, z thirds of bias_hh) and dnr_out float32 [N][G][H] = d(pre_n) * r, whose
+ * sum over N is the gradient of bias_hh's n third.  The gates are recomputed from gi. */
+int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const float* dh, int64_t n_envs,
+                        int32_t n_nets, int32_t hidden, float* dgi_out, float* dnr_out, void* stream);
+
 /* -- the path's one collective: episode statistics over NCCL --------------------- */
 /* libnccl.so.2 is bound with dlopen at first use (the process's own copy, e.g. PyTorch's); no link-time dependency.
  * `comm` is an ncclComm_t passed as void*: either one the caller already owns, or one made here:

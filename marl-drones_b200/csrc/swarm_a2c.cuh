@@ -5,7 +5,10 @@
 //                               returns = rewards + returns * gamma * masks        (float32, this operation order, no FMA)
 //                           for every (drone, env) column of a [T] rollout, plus the product of gamma*mask factors that
 //                           the backward pass needs (d returns_t / d last_values).
-// Both are streaming kernels (bound by HBM); neither is on the env-step path.
+//   gru_gates_fwd / bwd     the GRU cell of A2C/models.py:104 (`_, h = self.gru(x.unsqueeze(0))`, one step from h0 = 0) after
+//                           the input-side GEMM, for all 2D stacked nets: ten element-wise torch kernels (and their
+//                           autograd slices) folded into one pass each way.
+// All are streaming kernels (bound by HBM); none is on the env-step path.
 #pragma once
 #include "swarm_common.cuh"
 
@@ -83,6 +86,59 @@ __global__ void __launch_bounds__(256) nstep_returns_kernel(const float* __restr
         coef[(size_t)t * N + n] = c;
       }
     }
+  }
+}
+
+// GRU cell, one step from h0 = 0 (torch.nn.GRU gate order r, z, n; the hidden-side products vanish, bias_hh survives):
+//   r = sigmoid(gi_r + bh_r)   z = sigmoid(gi_z + bh_z)   n = tanh(gi_n + r * bh_n)   h = (1 - z) * n
+// gi float32 [N][G][3H] (x W_ih^T + b_ih, env-major as the GEMM leaves it), bhh float32 [G][3H], h float32 [G][N][H]
+// (net-major, contiguous: the layout the per-net batched GEMMs downstream want).  One thread per (n, g, j), j fastest:
+// reads and writes are contiguous runs of H floats.
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__global__ void __launch_bounds__(256) gru_gates_fwd_kernel(const float* __restrict__ gi, const float* __restrict__ bhh, long long N, int G, int H,
+                                                            float* __restrict__ h) {
+  const long long total = N * G * H;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(i % H);
+    const long long ng = i / H;
+    const int g = (int)(ng % G);
+    const long long n = ng / G;
+    const float* gp = gi + ng * 3 * H + j;
+    const float* bp = bhh + (size_t)g * 3 * H + j;
+    const float r = sigmoidf_(__ldcs(gp) + __ldg(bp));
+    const float z = sigmoidf_(__ldcs(gp + H) + __ldg(bp + H));
+    const float c = tanhf(__ldcs(gp + 2 * H) + r * __ldg(bp + 2 * H));
+    h[((size_t)g * N + n) * H + j] = (1.0f - z) * c;
+  }
+}
+
+// Backward of the above: dh [G][N][H] -> dgi [N][G][3H] (= the gradient of the pre-activations, which is also what b_ih and
+// the r / z thirds of b_hh accumulate) and dnr [N][G][H] = d(pre_n) * r, whose sum over n is the gradient of b_hh's n third.
+// The gates are recomputed from gi (cheaper than saving three activations per rollout step).
+__global__ void __launch_bounds__(256) gru_gates_bwd_kernel(const float* __restrict__ gi, const float* __restrict__ bhh, const float* __restrict__ dh,
+                                                            long long N, int G, int H, float* __restrict__ dgi, float* __restrict__ dnr) {
+  const long long total = N * G * H;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(i % H);
+    const long long ng = i / H;
+    const int g = (int)(ng % G);
+    const long long n = ng / G;
+    const float* gp = gi + ng * 3 * H + j;
+    const float* bp = bhh + (size_t)g * 3 * H + j;
+    const float bn = __ldg(bp + 2 * H);
+    const float r = sigmoidf_(__ldcs(gp) + __ldg(bp));
+    const float z = sigmoidf_(__ldcs(gp + H) + __ldg(bp + H));
+    const float c = tanhf(__ldcs(gp + 2 * H) + r * bn);
+    const float d = __ldcs(dh + ((size_t)g * N + n) * H + j);
+    const float dpn = d * (1.0f - z) * (1.0f - c * c);     // d pre_n
+    const float dpr = dpn * bn * r * (1.0f - r);            // d pre_r
+    const float dpz = -d * c * z * (1.0f - z);              // d pre_z
+    float* op = dgi + ng * 3 * H + j;
+    op[0] = dpr;
+    op[H] = dpz;
+    op[2 * H] = dpn;
+    dnr[i] = dpn * r;
   }
 }
 

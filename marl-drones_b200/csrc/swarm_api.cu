@@ -571,6 +571,31 @@ extern "C" int swarm_nstep_returns(const float* rewards, const uint8_t* dones, c
   return SWARM_OK;
 }
 
+extern "C" int swarm_gru_gates_fwd(const float* gi, const float* bias_hh, int64_t n_envs, int32_t n_nets, int32_t hidden, float* h_out, void* stream) {
+  if (!gi || !bias_hh || !h_out || n_envs < 1 || n_nets < 1 || hidden < 1) return SWARM_ERR_INVALID_ARG;
+  int sms = 0;
+  int rc = current_sm_count(&sms);
+  if (rc) return rc;
+  long long b = ((long long)n_envs * n_nets * hidden + 255) / 256;
+  if (b > (long long)sms * 16) b = (long long)sms * 16;
+  gru_gates_fwd_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(gi, bias_hh, n_envs, n_nets, hidden, h_out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const float* dh, int64_t n_envs, int32_t n_nets, int32_t hidden,
+                                   float* dgi_out, float* dnr_out, void* stream) {
+  if (!gi || !bias_hh || !dh || !dgi_out || !dnr_out || n_envs < 1 || n_nets < 1 || hidden < 1) return SWARM_ERR_INVALID_ARG;
+  int sms = 0;
+  int rc = current_sm_count(&sms);
+  if (rc) return rc;
+  long long b = ((long long)n_envs * n_nets * hidden + 255) / 256;
+  if (b > (long long)sms * 16) b = (long long)sms * 16;
+  gru_gates_bwd_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(gi, bias_hh, dh, n_envs, n_nets, hidden, dgi_out, dnr_out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ NCCL (statistics only)
 // The path's one collective: ncclAllReduce(SUM, int64[8]) of the episode statistics, 64 B per rank.  libnccl is
 // bound at run time (dlopen of the copy the process already carries — PyTorch's — else the system one), so the library has no

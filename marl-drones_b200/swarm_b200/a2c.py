@@ -177,12 +177,16 @@ class BatchedPolicy(nn.Module):
         x = (obs - mu) / std
         # GRU, one step from h0 = 0 (models.py:104): the hidden-side products vanish, only bias_hh survives
         wih, bih, bhh = self.gru__weight_ih_l0, self.gru__bias_ih_l0, self.gru__bias_hh_l0
-        gi = torch.addmm(bih.reshape(1, G * 3 * H), x, wih.reshape(G * 3 * H, H).t()).view(N, G, 3 * H).transpose(0, 1)   # [G, N, 3H]
-        bh = bhh.unsqueeze(1)
-        r = torch.sigmoid(gi[..., :H] + bh[..., :H])
-        z = torch.sigmoid(gi[..., H:2 * H] + bh[..., H:2 * H])
-        n = torch.tanh(gi[..., 2 * H:] + r * bh[..., 2 * H:])
-        h = (1.0 - z) * n                                                   # + z * h0, h0 = 0
+        gi = torch.addmm(bih.reshape(1, G * 3 * H), x, wih.reshape(G * 3 * H, H).t())                                     # [N, G*3H]
+        if gi.is_cuda and gi.dtype == torch.float32:
+            h = _GruGates.apply(gi, bhh)                                    # one fused pass each way (swarm_gru_gates_fwd / _bwd)
+        else:                                                               # float64 / CPU checks of the same arithmetic
+            gi = gi.view(N, G, 3 * H).transpose(0, 1)                       # [G, N, 3H]
+            bh = bhh.unsqueeze(1)
+            r = torch.sigmoid(gi[..., :H] + bh[..., :H])
+            z = torch.sigmoid(gi[..., H:2 * H] + bh[..., H:2 * H])
+            n = torch.tanh(gi[..., 2 * H:] + r * bh[..., 2 * H:])
+            h = (1.0 - z) * n                                               # + z * h0, h0 = 0
         s = self._lin(h, "attn1.v")                                         # attn_mask == 1  (models.py:67-70)
         s = self._lin(s, "state_input", relu=True)
         s = F.normalize(s, dim=-1)                                          # models.py:108 (L2 over features, eps 1e-12)
@@ -210,6 +214,33 @@ def sample_actions(logits, seed, step, env_id_base=0, out=None):
     check(_lib.lib().swarm_sample_actions(logits.data_ptr(), D, N, A, int(seed) & (2 ** 64 - 1), int(step) & 0xffffffff,
                                           int(env_id_base), out.data_ptr(), _raw_stream(logits.device.index)))
     return out
+
+
+class _GruGates(torch.autograd.Function):
+    """h = GRU cell gates at h0 = 0 (A2C/models.py:104): gi [N, G*3H] (x W_ih^T + b_ih), bias_hh [G, 3H] -> h [G, N, H]."""
+
+    @staticmethod
+    def forward(ctx, gi, bhh):
+        G, H3 = bhh.shape
+        H, N = H3 // 3, gi.shape[0]
+        gi_c, bhh_c = gi.detach().contiguous(), bhh.detach().contiguous()
+        h = torch.empty((G, N, H), dtype=torch.float32, device=gi.device)
+        check(_lib.lib().swarm_gru_gates_fwd(gi_c.data_ptr(), bhh_c.data_ptr(), N, G, H, h.data_ptr(), _raw_stream(gi.device.index)))
+        ctx.save_for_backward(gi_c, bhh_c)
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        gi, bhh = ctx.saved_tensors
+        G, H3 = bhh.shape
+        H, N = H3 // 3, gi.shape[0]
+        dh = dh.contiguous()
+        dgi = torch.empty_like(gi)
+        dnr = torch.empty((N, G, H), dtype=torch.float32, device=gi.device)
+        check(_lib.lib().swarm_gru_gates_bwd(gi.data_ptr(), bhh.data_ptr(), dh.data_ptr(), N, G, H, dgi.data_ptr(), dnr.data_ptr(),
+                                             _raw_stream(gi.device.index)))
+        dbhh = torch.cat([dgi.view(N, G, 3, H)[:, :, :2].sum(0), dnr.sum(0).unsqueeze(1)], dim=1).reshape(G, H3)
+        return dgi, dbhh
 
 
 class _NStepReturns(torch.autograd.Function):

@@ -175,3 +175,29 @@ def test_icm_bonus_iteration_equals_reference_train():
         for k, w in zip(keys, want):
             assert _close(ac.digest(gd[k])[lin], w[lin], max(scale, np.abs(w[lin]).max())), (i, k)
     env.close()
+
+
+@pytest.mark.parametrize("N,G,H", [(1, 2, 25), (37, 6, 100), (513, 16, 36)])
+def test_fused_gru_gates_match_the_torch_expression(N, G, H):
+    """swarm_gru_gates_fwd / _bwd against the element-wise definition (torch.nn.GRU cell at h0 = 0, A2C/models.py:104) in
+    float64: values within 1e-6, gradients of gi and bias_hh within 1e-5 relative."""
+    from swarm_b200.a2c import _GruGates
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    gi = (torch.randn((N, G * 3 * H), device="cuda", generator=gen) * 1.5).requires_grad_(True)
+    bhh = torch.randn((G, 3 * H), device="cuda", generator=gen).requires_grad_(True)
+    w = torch.randn((G, N, H), device="cuda", generator=gen)
+    h = _GruGates.apply(gi, bhh)
+    assert h.shape == (G, N, H) and h.is_contiguous()
+    (h * w).sum().backward()
+    gi64 = gi.detach().double().requires_grad_(True)
+    bh64 = bhh.detach().double().requires_grad_(True)
+    g3 = gi64.view(N, G, 3 * H).transpose(0, 1)
+    b3 = bh64.unsqueeze(1)
+    r = torch.sigmoid(g3[..., :H] + b3[..., :H])
+    z = torch.sigmoid(g3[..., H:2 * H] + b3[..., H:2 * H])
+    n = torch.tanh(g3[..., 2 * H:] + r * b3[..., 2 * H:])
+    h64 = (1.0 - z) * n
+    (h64 * w.double()).sum().backward()
+    assert torch.allclose(h.double(), h64, rtol=1e-6, atol=1e-6)
+    assert torch.allclose(gi.grad.double(), gi64.grad, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(bhh.grad.double(), bh64.grad, rtol=1e-5, atol=1e-5 * max(1.0, N ** 0.5))
