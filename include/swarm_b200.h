@@ -200,6 +200,15 @@ int swarm_gru_gates_fwd(const float* gi, const float* bias_hh, int64_t n_envs, i
 int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const float* dh, int64_t n_envs,
                         int32_t n_nets, int32_t hidden, float* dgi_out, float* dnr_out, void* stream);
 
+/* relu + F.normalize(dim=-1) of the policy's state embedding (A2C/models.py:107-108) in one pass:
+ *   y = max(x, 0), out = y / max(||y||_2, eps)      x, out float32 [rows][features], 16 B aligned. */
+int swarm_relu_l2norm_fwd(const float* x, int64_t rows, int32_t features, float eps, float* out,
+                          void* stream);
+/* Its backward (y and the norm are recomputed from x): grad_x = (g / d - y (g.y) / d^3) where x > 0, d = max(||y||, eps);
+ * rows whose norm is below eps get g / eps, as torch's clamp_min does. */
+int swarm_relu_l2norm_bwd(const float* x, const float* grad_out, int64_t rows, int32_t features,
+                          float eps, float* grad_x, void* stream);
+
 /* -- the path's one collective: episode statistics over NCCL --------------------- */
 /* libnccl.so.2 is bound with dlopen at first use (the process's own copy, e.g. PyTorch's); no link-time dependency.
  * `comm` is an ncclComm_t passed as void*: either one the caller already owns, or one made here:

@@ -142,4 +142,85 @@ __global__ void __launch_bounds__(256) gru_gates_bwd_kernel(const float* __restr
   }
 }
 
+// relu followed by F.normalize(dim=-1) (A2C/models.py:107-108: `F.relu(self.state_input(...))`, `F.normalize(...)`):
+//   y = max(x, 0)   o = y / max(||y||_2, eps)
+// x, o float32 [rows][F], one warp per row (a row is read twice; the second read hits L1).  F % 4 == 0 takes 128-bit accesses.
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(256) relu_l2norm_fwd_kernel(const float* __restrict__ x, long long rows, int F, float eps, float* __restrict__ o) {
+  const int lane = threadIdx.x & 31;
+  const long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w0; r < rows; r += nw) {
+    const float* xr = x + (size_t)r * F;
+    float* orow = o + (size_t)r * F;
+    float ss = 0.f;
+    if ((F & 3) == 0) {
+      for (int k = lane * 4; k < F; k += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xr + k);
+        const float a = fmaxf(v.x, 0.f), b = fmaxf(v.y, 0.f), c = fmaxf(v.z, 0.f), d = fmaxf(v.w, 0.f);
+        ss += a * a + b * b + c * c + d * d;
+      }
+    } else {
+      for (int k = lane; k < F; k += 32) { const float a = fmaxf(xr[k], 0.f); ss += a * a; }
+    }
+    const float inv = 1.0f / fmaxf(sqrtf(warp_sum(ss)), eps);
+    if ((F & 3) == 0) {
+      for (int k = lane * 4; k < F; k += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xr + k);
+        __stcs(reinterpret_cast<float4*>(orow + k), make_float4(fmaxf(v.x, 0.f) * inv, fmaxf(v.y, 0.f) * inv, fmaxf(v.z, 0.f) * inv, fmaxf(v.w, 0.f) * inv));
+      }
+    } else {
+      for (int k = lane; k < F; k += 32) orow[k] = fmaxf(xr[k], 0.f) * inv;
+    }
+  }
+}
+
+// Backward: with d = max(||y||, eps) and g = d loss / d o:
+//   ||y|| >  eps:  dy = g / d - y * (g . y) / d^3        ||y|| <= eps:  dy = g / eps   (the clamp blocks the norm's path)
+//   dx = dy where x > 0, else 0
+__global__ void __launch_bounds__(256) relu_l2norm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g, long long rows, int F, float eps,
+                                                              float* __restrict__ dx) {
+  const int lane = threadIdx.x & 31;
+  const long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w0; r < rows; r += nw) {
+    const float* xr = x + (size_t)r * F;
+    const float* gr = g + (size_t)r * F;
+    float* dr = dx + (size_t)r * F;
+    float ss = 0.f, gy = 0.f;
+    if ((F & 3) == 0) {
+      for (int k = lane * 4; k < F; k += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xr + k);
+        const float4 u = *reinterpret_cast<const float4*>(gr + k);
+        const float a = fmaxf(v.x, 0.f), b = fmaxf(v.y, 0.f), c = fmaxf(v.z, 0.f), d = fmaxf(v.w, 0.f);
+        ss += a * a + b * b + c * c + d * d;
+        gy += u.x * a + u.y * b + u.z * c + u.w * d;
+      }
+    } else {
+      for (int k = lane; k < F; k += 32) { const float a = fmaxf(xr[k], 0.f); ss += a * a; gy += gr[k] * a; }
+    }
+    const float nrm = sqrtf(warp_sum(ss));
+    gy = warp_sum(gy);
+    const float d = fmaxf(nrm, eps), inv = 1.0f / d;
+    const float c3 = nrm > eps ? gy * inv * inv * inv : 0.f;
+    if ((F & 3) == 0) {
+      for (int k = lane * 4; k < F; k += 128) {
+        const float4 v = *reinterpret_cast<const float4*>(xr + k);
+        const float4 u = *reinterpret_cast<const float4*>(gr + k);
+        float4 t;
+        t.x = v.x > 0.f ? u.x * inv - v.x * c3 : 0.f;
+        t.y = v.y > 0.f ? u.y * inv - v.y * c3 : 0.f;
+        t.z = v.z > 0.f ? u.z * inv - v.z * c3 : 0.f;
+        t.w = v.w > 0.f ? u.w * inv - v.w * c3 : 0.f;
+        __stcs(reinterpret_cast<float4*>(dr + k), t);
+      }
+    } else {
+      for (int k = lane; k < F; k += 32) dr[k] = xr[k] > 0.f ? gr[k] * inv - xr[k] * c3 : 0.f;
+    }
+  }
+}
+
 }  // namespace swarm

@@ -596,6 +596,36 @@ extern "C" int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const 
   return SWARM_OK;
 }
 
+static int row_kernel_blocks(int64_t rows, int* blocks) {
+  int sms = 0;
+  int rc = current_sm_count(&sms);
+  if (rc) return rc;
+  long long b = (rows + 7) / 8;   // one warp per row, 8 warps per block
+  if (b > (long long)sms * 16) b = (long long)sms * 16;
+  *blocks = (int)b;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_relu_l2norm_fwd(const float* x, int64_t rows, int32_t features, float eps, float* out, void* stream) {
+  if (!x || !out || rows < 1 || features < 1 || (((uintptr_t)x | (uintptr_t)out) & 15)) return SWARM_ERR_INVALID_ARG;
+  int b = 0;
+  int rc = row_kernel_blocks(rows, &b);
+  if (rc) return rc;
+  relu_l2norm_fwd_kernel<<<b, 256, 0, (cudaStream_t)stream>>>(x, rows, features, eps, out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_relu_l2norm_bwd(const float* x, const float* grad_out, int64_t rows, int32_t features, float eps, float* grad_x, void* stream) {
+  if (!x || !grad_out || !grad_x || rows < 1 || features < 1 || (((uintptr_t)x | (uintptr_t)grad_out | (uintptr_t)grad_x) & 15)) return SWARM_ERR_INVALID_ARG;
+  int b = 0;
+  int rc = row_kernel_blocks(rows, &b);
+  if (rc) return rc;
+  relu_l2norm_bwd_kernel<<<b, 256, 0, (cudaStream_t)stream>>>(x, grad_out, rows, features, eps, grad_x);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ NCCL (statistics only)
 // The path's one collective: ncclAllReduce(SUM, int64[8]) of the episode statistics, 64 B per rank.  libnccl is
 // bound at run time (dlopen of the copy the process already carries — PyTorch's — else the system one), so the library has no

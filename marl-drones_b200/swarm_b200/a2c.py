@@ -159,7 +159,7 @@ class BatchedPolicy(nn.Module):
     # ---------------------------------------------------------------------------------- forward
     def _lin(self, x, key, relu=False):
         w, b = getattr(self, _pname(key + ".weight")), getattr(self, _pname(key + ".bias"))
-        y = torch.baddbmm(b.unsqueeze(1), x, w.transpose(1, 2))
+        y = _StackedLinear.apply(x, w, b)
         return F.relu(y) if relu else y
 
     def forward(self, obs, drone_pos=None):
@@ -188,8 +188,11 @@ class BatchedPolicy(nn.Module):
             n = torch.tanh(gi[..., 2 * H:] + r * bh[..., 2 * H:])
             h = (1.0 - z) * n                                               # + z * h0, h0 = 0
         s = self._lin(h, "attn1.v")                                         # attn_mask == 1  (models.py:67-70)
-        s = self._lin(s, "state_input", relu=True)
-        s = F.normalize(s, dim=-1)                                          # models.py:108 (L2 over features, eps 1e-12)
+        s = self._lin(s, "state_input")
+        if s.is_cuda and s.dtype == torch.float32:
+            s = _ReluL2Norm.apply(s)                                        # relu + F.normalize fused (swarm_relu_l2norm_fwd / _bwd)
+        else:
+            s = F.normalize(F.relu(s), dim=-1)                              # models.py:107-108 (L2 over features, eps 1e-12)
         s = self._lin(s, "dense1", relu=True)
         s = self._lin(s, "attn2.v")
         s = self._lin(s, "dense2", relu=True)
@@ -241,6 +244,59 @@ class _GruGates(torch.autograd.Function):
                                              _raw_stream(gi.device.index)))
         dbhh = torch.cat([dgi.view(N, G, 3, H)[:, :, :2].sum(0), dnr.sum(0).unsqueeze(1)], dim=1).reshape(G, H3)
         return dgi, dbhh
+
+
+class _StackedLinear(torch.autograd.Function):
+    """y[g] = x[g] @ w[g].T + b[g] for the 2D stacked nets: x [G, N, in], w [G, out, in], b [G, out] -> y [G, N, out].
+
+    Same forward as `torch.baddbmm`; the backward computes the weight gradient as a split-K batched GEMM.  For N in the tens
+    of thousands the plain `dy^T x` is G small (out x in) products with a huge reduction dimension, which cuBLAS runs as a
+    handful of 32 x 32 tiles (a few hundred CTAs on 148 SMs); splitting N into S slices gives G * S independent products
+    and one cheap sum over S."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        return torch.baddbmm(b.unsqueeze(1), x, w.transpose(1, 2))
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        G, N, fin = x.shape
+        fout = w.shape[1]
+        dy = dy.contiguous()
+        dx = torch.bmm(dy, w) if ctx.needs_input_grad[0] else None
+        S = 1
+        while S < 16 and N % (2 * S) == 0 and N // (2 * S) >= 512:
+            S *= 2
+        if S > 1:
+            xc = x.contiguous()
+            dw = torch.bmm(dy.view(G * S, N // S, fout).transpose(1, 2), xc.view(G * S, N // S, fin)).view(G, S, fout, fin).sum(1)
+        else:
+            dw = torch.bmm(dy.transpose(1, 2), x)
+        return dx, dw, dy.sum(1)
+
+
+class _ReluL2Norm(torch.autograd.Function):
+    """F.normalize(F.relu(x), dim=-1) (A2C/models.py:107-108), x [..., F] float32 on the GPU."""
+
+    @staticmethod
+    def forward(ctx, x):
+        xc = x.detach().contiguous()
+        out = torch.empty_like(xc)
+        Fdim = xc.shape[-1]
+        check(_lib.lib().swarm_relu_l2norm_fwd(xc.data_ptr(), xc.numel() // Fdim, Fdim, 1e-12, out.data_ptr(), _raw_stream(x.device.index)))
+        ctx.save_for_backward(xc)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (xc,) = ctx.saved_tensors
+        g = g.contiguous()
+        dx = torch.empty_like(xc)
+        Fdim = xc.shape[-1]
+        check(_lib.lib().swarm_relu_l2norm_bwd(xc.data_ptr(), g.data_ptr(), xc.numel() // Fdim, Fdim, 1e-12, dx.data_ptr(), _raw_stream(g.device.index)))
+        return dx
 
 
 class _NStepReturns(torch.autograd.Function):

@@ -201,3 +201,24 @@ def test_fused_gru_gates_match_the_torch_expression(N, G, H):
     assert torch.allclose(h.double(), h64, rtol=1e-6, atol=1e-6)
     assert torch.allclose(gi.grad.double(), gi64.grad, rtol=1e-5, atol=1e-6)
     assert torch.allclose(bhh.grad.double(), bh64.grad, rtol=1e-5, atol=1e-5 * max(1.0, N ** 0.5))
+
+
+@pytest.mark.parametrize("shape", [(3, 5, 256), (2, 129, 100), (1, 7, 33)])
+def test_fused_relu_l2norm_matches_torch(shape):
+    """swarm_relu_l2norm_fwd / _bwd against F.normalize(F.relu(x), dim=-1) in float64 (A2C/models.py:107-108), including a
+    row that relu zeroes completely (norm below eps: output 0, gradient blocked by the relu)."""
+    import torch.nn.functional as F
+    from swarm_b200.a2c import _ReluL2Norm
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(shape, device="cuda", generator=gen)
+    x[0, 0] = -x[0, 0].abs() - 0.1                      # an all-negative row
+    x = x.requires_grad_(True)
+    w = torch.randn(shape, device="cuda", generator=gen)
+    o = _ReluL2Norm.apply(x)
+    (o * w).sum().backward()
+    x64 = x.detach().double().requires_grad_(True)
+    o64 = F.normalize(F.relu(x64), dim=-1)
+    (o64 * w.double()).sum().backward()
+    assert torch.allclose(o.double(), o64, rtol=1e-6, atol=1e-7)
+    assert torch.allclose(x.grad.double(), x64.grad, rtol=1e-5, atol=1e-6)
+    assert float(o.detach()[0, 0].abs().max()) == 0.0 and float(x.grad[0, 0].abs().max()) == 0.0
