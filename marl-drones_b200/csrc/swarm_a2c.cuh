@@ -98,6 +98,29 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf
 
 __global__ void __launch_bounds__(256) gru_gates_fwd_kernel(const float* __restrict__ gi, const float* __restrict__ bhh, long long N, int G, int H,
                                                             float* __restrict__ h) {
+  if ((H & 3) == 0) {   // four consecutive hidden units per thread: 128-bit accesses throughout
+    const int H4 = H >> 2;
+    const long long total4 = N * G * H4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
+      const int j = (int)(i % H4) * 4;
+      const long long ng = i / H4;
+      const int g = (int)(ng % G);
+      const long long n = ng / G;
+      const float* gp = gi + ng * 3 * H + j;
+      const float* bp = bhh + (size_t)g * 3 * H + j;
+      const float4 gr = __ldcs(reinterpret_cast<const float4*>(gp)), gz = __ldcs(reinterpret_cast<const float4*>(gp + H));
+      const float4 gn = __ldcs(reinterpret_cast<const float4*>(gp + 2 * H));
+      const float4 br = __ldg(reinterpret_cast<const float4*>(bp)), bz = __ldg(reinterpret_cast<const float4*>(bp + H));
+      const float4 bn = __ldg(reinterpret_cast<const float4*>(bp + 2 * H));
+      float4 o;
+      o.x = (1.0f - sigmoidf_(gz.x + bz.x)) * tanhf(gn.x + sigmoidf_(gr.x + br.x) * bn.x);
+      o.y = (1.0f - sigmoidf_(gz.y + bz.y)) * tanhf(gn.y + sigmoidf_(gr.y + br.y) * bn.y);
+      o.z = (1.0f - sigmoidf_(gz.z + bz.z)) * tanhf(gn.z + sigmoidf_(gr.z + br.z) * bn.z);
+      o.w = (1.0f - sigmoidf_(gz.w + bz.w)) * tanhf(gn.w + sigmoidf_(gr.w + br.w) * bn.w);
+      *reinterpret_cast<float4*>(h + ((size_t)g * N + n) * H + j) = o;
+    }
+    return;
+  }
   const long long total = N * G * H;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int j = (int)(i % H);
@@ -116,8 +139,45 @@ __global__ void __launch_bounds__(256) gru_gates_fwd_kernel(const float* __restr
 // Backward of the above: dh [G][N][H] -> dgi [N][G][3H] (= the gradient of the pre-activations, which is also what b_ih and
 // the r / z thirds of b_hh accumulate) and dnr [N][G][H] = d(pre_n) * r, whose sum over n is the gradient of b_hh's n third.
 // The gates are recomputed from gi (cheaper than saving three activations per rollout step).
+__device__ __forceinline__ void gru_gate_grad(float gr, float gz, float gn, float br, float bz, float bn, float d, float& dpr, float& dpz,
+                                              float& dpn, float& dnr) {
+  const float r = sigmoidf_(gr + br), z = sigmoidf_(gz + bz), c = tanhf(gn + r * bn);
+  dpn = d * (1.0f - z) * (1.0f - c * c);     // d pre_n
+  dpr = dpn * bn * r * (1.0f - r);            // d pre_r
+  dpz = -d * c * z * (1.0f - z);              // d pre_z
+  dnr = dpn * r;
+}
+
 __global__ void __launch_bounds__(256) gru_gates_bwd_kernel(const float* __restrict__ gi, const float* __restrict__ bhh, const float* __restrict__ dh,
                                                             long long N, int G, int H, float* __restrict__ dgi, float* __restrict__ dnr) {
+  if ((H & 3) == 0) {
+    const int H4 = H >> 2;
+    const long long total4 = N * G * H4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
+      const int j = (int)(i % H4) * 4;
+      const long long ng = i / H4;
+      const int g = (int)(ng % G);
+      const long long n = ng / G;
+      const float* gp = gi + ng * 3 * H + j;
+      const float* bp = bhh + (size_t)g * 3 * H + j;
+      const float4 gr = __ldcs(reinterpret_cast<const float4*>(gp)), gz = __ldcs(reinterpret_cast<const float4*>(gp + H));
+      const float4 gn = __ldcs(reinterpret_cast<const float4*>(gp + 2 * H));
+      const float4 br = __ldg(reinterpret_cast<const float4*>(bp)), bz = __ldg(reinterpret_cast<const float4*>(bp + H));
+      const float4 bn = __ldg(reinterpret_cast<const float4*>(bp + 2 * H));
+      const float4 d = __ldcs(reinterpret_cast<const float4*>(dh + ((size_t)g * N + n) * H + j));
+      float4 o_r, o_z, o_n, o_a;
+      gru_gate_grad(gr.x, gz.x, gn.x, br.x, bz.x, bn.x, d.x, o_r.x, o_z.x, o_n.x, o_a.x);
+      gru_gate_grad(gr.y, gz.y, gn.y, br.y, bz.y, bn.y, d.y, o_r.y, o_z.y, o_n.y, o_a.y);
+      gru_gate_grad(gr.z, gz.z, gn.z, br.z, bz.z, bn.z, d.z, o_r.z, o_z.z, o_n.z, o_a.z);
+      gru_gate_grad(gr.w, gz.w, gn.w, br.w, bz.w, bn.w, d.w, o_r.w, o_z.w, o_n.w, o_a.w);
+      float* op = dgi + ng * 3 * H + j;
+      *reinterpret_cast<float4*>(op) = o_r;
+      *reinterpret_cast<float4*>(op + H) = o_z;
+      *reinterpret_cast<float4*>(op + 2 * H) = o_n;
+      *reinterpret_cast<float4*>(dnr + ng * H + j) = o_a;
+    }
+    return;
+  }
   const long long total = N * G * H;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int j = (int)(i % H);
@@ -126,19 +186,9 @@ __global__ void __launch_bounds__(256) gru_gates_bwd_kernel(const float* __restr
     const long long n = ng / G;
     const float* gp = gi + ng * 3 * H + j;
     const float* bp = bhh + (size_t)g * 3 * H + j;
-    const float bn = __ldg(bp + 2 * H);
-    const float r = sigmoidf_(__ldcs(gp) + __ldg(bp));
-    const float z = sigmoidf_(__ldcs(gp + H) + __ldg(bp + H));
-    const float c = tanhf(__ldcs(gp + 2 * H) + r * bn);
-    const float d = __ldcs(dh + ((size_t)g * N + n) * H + j);
-    const float dpn = d * (1.0f - z) * (1.0f - c * c);     // d pre_n
-    const float dpr = dpn * bn * r * (1.0f - r);            // d pre_r
-    const float dpz = -d * c * z * (1.0f - z);              // d pre_z
     float* op = dgi + ng * 3 * H + j;
-    op[0] = dpr;
-    op[H] = dpz;
-    op[2 * H] = dpn;
-    dnr[i] = dpn * r;
+    gru_gate_grad(__ldcs(gp), __ldcs(gp + H), __ldcs(gp + 2 * H), __ldg(bp), __ldg(bp + H), __ldg(bp + 2 * H),
+                  __ldcs(dh + ((size_t)g * N + n) * H + j), op[0], op[H], op[2 * H], dnr[i]);
   }
 }
 

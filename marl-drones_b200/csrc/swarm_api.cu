@@ -573,6 +573,7 @@ extern "C" int swarm_nstep_returns(const float* rewards, const uint8_t* dones, c
 
 extern "C" int swarm_gru_gates_fwd(const float* gi, const float* bias_hh, int64_t n_envs, int32_t n_nets, int32_t hidden, float* h_out, void* stream) {
   if (!gi || !bias_hh || !h_out || n_envs < 1 || n_nets < 1 || hidden < 1) return SWARM_ERR_INVALID_ARG;
+  if ((hidden & 3) == 0 && (((uintptr_t)gi | (uintptr_t)bias_hh | (uintptr_t)h_out) & 15)) return SWARM_ERR_INVALID_ARG;   // 128-bit path
   int sms = 0;
   int rc = current_sm_count(&sms);
   if (rc) return rc;
@@ -586,6 +587,7 @@ extern "C" int swarm_gru_gates_fwd(const float* gi, const float* bias_hh, int64_
 extern "C" int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const float* dh, int64_t n_envs, int32_t n_nets, int32_t hidden,
                                    float* dgi_out, float* dnr_out, void* stream) {
   if (!gi || !bias_hh || !dh || !dgi_out || !dnr_out || n_envs < 1 || n_nets < 1 || hidden < 1) return SWARM_ERR_INVALID_ARG;
+  if ((hidden & 3) == 0 && (((uintptr_t)gi | (uintptr_t)bias_hh | (uintptr_t)dh | (uintptr_t)dgi_out | (uintptr_t)dnr_out) & 15)) return SWARM_ERR_INVALID_ARG;
   int sms = 0;
   int rc = current_sm_count(&sms);
   if (rc) return rc;
