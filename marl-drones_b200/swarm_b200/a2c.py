@@ -162,6 +162,8 @@ class BatchedPolicy(nn.Module):
         y = _StackedLinear.apply(x, w, b)
         return F.relu(y) if relu else y
 
+    fused = True   # float32 CUDA tensors go through swarm_gru_gates_* / swarm_relu_l2norm_*; False keeps the op-by-op torch expression (checks)
+
     def forward(self, obs, drone_pos=None):
         """obs float [N, obs_size] (one row per env) -> (logits [D, N, A], values [D, N, 1]).
 
@@ -178,7 +180,7 @@ class BatchedPolicy(nn.Module):
         # GRU, one step from h0 = 0 (models.py:104): the hidden-side products vanish, only bias_hh survives
         wih, bih, bhh = self.gru__weight_ih_l0, self.gru__bias_ih_l0, self.gru__bias_hh_l0
         gi = torch.addmm(bih.reshape(1, G * 3 * H), x, wih.reshape(G * 3 * H, H).t())                                     # [N, G*3H]
-        if gi.is_cuda and gi.dtype == torch.float32:
+        if self.fused and gi.is_cuda and gi.dtype == torch.float32:
             h = _GruGates.apply(gi, bhh)                                    # one fused pass each way (swarm_gru_gates_fwd / _bwd)
         else:                                                               # float64 / CPU checks of the same arithmetic
             gi = gi.view(N, G, 3 * H).transpose(0, 1)                       # [G, N, 3H]
@@ -189,7 +191,7 @@ class BatchedPolicy(nn.Module):
             h = (1.0 - z) * n                                               # + z * h0, h0 = 0
         s = self._lin(h, "attn1.v")                                         # attn_mask == 1  (models.py:67-70)
         s = self._lin(s, "state_input")
-        if s.is_cuda and s.dtype == torch.float32:
+        if self.fused and s.is_cuda and s.dtype == torch.float32:
             s = _ReluL2Norm.apply(s)                                        # relu + F.normalize fused (swarm_relu_l2norm_fwd / _bwd)
         else:
             s = F.normalize(F.relu(s), dim=-1)                              # models.py:107-108 (L2 over features, eps 1e-12)

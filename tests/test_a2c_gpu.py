@@ -222,3 +222,45 @@ def test_fused_relu_l2norm_matches_torch(shape):
     assert torch.allclose(o.double(), o64, rtol=1e-6, atol=1e-7)
     assert torch.allclose(x.grad.double(), x64.grad, rtol=1e-5, atol=1e-6)
     assert float(o.detach()[0, 0].abs().max()) == 0.0 and float(x.grad[0, 0].abs().max()) == 0.0
+
+
+def test_fused_policy_equals_float64_policy_at_cfg4_size():
+    """BASELINE configs[3] shape (16 384 envs x 8 drones, 10x10): the float32 CUDA policy — fused GRU gates, fused relu +
+    normalize, split-K weight gradients — against the same stacked weights evaluated op by op in float64 on the same inputs.
+    Outputs within 2e-5.  Gradients of a scalar probe loss: float32 rounding is amplified by the 1 / ||.|| of F.normalize, so
+    the yardstick is the op-by-op float32 torch expression (`fused = False`) measured against float64 the same way — the fused
+    path may not be further from float64 than 2x that (+1e-4 of the tensor's largest entry)."""
+    N, D, H = 16384, 8, 100
+    torch.manual_seed(3)
+    pol = BatchedPolicy(H, D, 4, device="cuda")
+    pol64 = BatchedPolicy(H, D, 4, device="cuda").double()
+    with torch.no_grad():
+        for a, b in zip(pol64.parameters(), pol.parameters()):
+            a.copy_(b.double())
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    obs = torch.randint(0, 3, (N, H), device="cuda", generator=gen).float()
+    obs[obs == 2] = 5.0                                   # cells are 0 / 1 / U
+    lw = torch.randn((D, N, 4), device="cuda", generator=gen)
+    vw = torch.randn((D, N, 1), device="cuda", generator=gen)
+
+    def grads(p, x, fused):
+        p.fused = fused
+        for prm in p.parameters():
+            prm.grad = None
+        lg, vl = p(x)
+        ((lg * lw.to(lg.dtype)).sum() + (vl * vw.to(vl.dtype)).sum()).backward()
+        return lg.detach(), vl.detach(), [None if prm.grad is None else prm.grad.double().clone() for prm in p.parameters()]
+
+    lg64, vl64, g64 = grads(pol64, obs.double(), False)
+    lgu, vlu, gu = grads(pol, obs, False)
+    lgf, vlf, gf = grads(pol, obs, True)
+    assert torch.allclose(lgf.double(), lg64, rtol=0, atol=2e-5) and torch.allclose(vlf.double(), vl64, rtol=0, atol=2e-5)
+    checked = 0
+    for (name, _), a64, au, af in zip(pol.named_parameters(), g64, gu, gf):
+        if a64 is None or af is None or float(a64.abs().max()) == 0.0:
+            continue
+        scale = float(a64.abs().max())
+        err_f, err_u = float((af - a64).abs().max()) / scale, float((au - a64).abs().max()) / scale
+        assert err_f <= 2.0 * err_u + 1e-4, (name, err_f, err_u)
+        checked += 1
+    assert checked >= 16
