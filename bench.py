@@ -291,7 +291,7 @@ def run_a2c(args, rank, world, local):
             "e2e": {"value": agent_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4, "steps": K,
                     "ms_per_step": e2e_ms / K, "api": "A2CTrainer.train_iteration() + loss.item()"},
             "rollout_only": {"value": agent_steps / (roll_ms * 1e-3), "unit": UNIT, "ms_per_step": roll_ms / K, "what": "no autograd, no update: policy fwd + sample + env step"},
-            "gpu_launches": int(env_launches + K * (T + 1) + K * 4 * (T + 1)), "gpu_launches_note": "swarm_step + swarm_sample_actions per rollout step, swarm_nstep_returns + reset per iteration, swarm_gru_gates_fwd/_bwd + swarm_relu_l2norm_fwd/_bwd per policy call (T + 1 per iteration; torch/cuBLAS kernels not counted)",
+            "gpu_launches": int(env_launches + K * (T + 1) + K * 11 * (T + 1)), "gpu_launches_note": "swarm_step + swarm_sample_actions per rollout step, swarm_nstep_returns + reset per iteration, swarm_gru_gates_fwd/_bwd + swarm_relu_l2norm_fwd/_bwd + 7 swarm_bias_act per policy call (T + 1 per iteration; torch/cuBLAS kernels not counted)",
             "clocks": clocks,
             "cpu_baseline": {"value": 47.2, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified A2C/train.py::train(), 250 env-steps, 10x10, 8 drones, MLP, measured in the build container (cannot travel to the GPU box)"},
         }

@@ -159,8 +159,7 @@ class BatchedPolicy(nn.Module):
     # ---------------------------------------------------------------------------------- forward
     def _lin(self, x, key, relu=False):
         w, b = getattr(self, _pname(key + ".weight")), getattr(self, _pname(key + ".bias"))
-        y = _StackedLinear.apply(x, w, b)
-        return F.relu(y) if relu else y
+        return _StackedLinear.apply(x, w, b, bool(relu), bool(self.fused))
 
     fused = True   # float32 CUDA tensors go through swarm_gru_gates_* / swarm_relu_l2norm_*; False keeps the op-by-op torch expression (checks)
 
@@ -257,16 +256,28 @@ class _StackedLinear(torch.autograd.Function):
     and one cheap sum over S."""
 
     @staticmethod
-    def forward(ctx, x, w, b):
-        ctx.save_for_backward(x, w)
-        return torch.baddbmm(b.unsqueeze(1), x, w.transpose(1, 2))
+    def forward(ctx, x, w, b, relu=False, fused=True):
+        G, N, _ = x.shape
+        if fused and x.is_cuda and x.dtype == torch.float32:
+            y = torch.bmm(x, w.transpose(1, 2))                             # plain GEMM, then bias (+ relu) in one in-place pass
+            check(_lib.lib().swarm_bias_act(y.data_ptr(), b.detach().contiguous().data_ptr(), G, N, y.shape[2], int(relu),
+                                            _raw_stream(x.device.index)))
+        else:
+            y = torch.baddbmm(b.unsqueeze(1), x, w.transpose(1, 2))
+            if relu:
+                y = F.relu(y)
+        ctx.relu = relu
+        ctx.save_for_backward(x, w, y if relu else None)
+        return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, w = ctx.saved_tensors
+        x, w, y = ctx.saved_tensors
         G, N, fin = x.shape
         fout = w.shape[1]
         dy = dy.contiguous()
+        if ctx.relu:
+            dy = torch.ops.aten.threshold_backward(dy, y, 0)               # relu'(pre) = [y > 0]
         dx = torch.bmm(dy, w) if ctx.needs_input_grad[0] else None
         S = 1
         while S < 16 and N % (2 * S) == 0 and N // (2 * S) >= 512:
@@ -276,7 +287,7 @@ class _StackedLinear(torch.autograd.Function):
             dw = torch.bmm(dy.view(G * S, N // S, fout).transpose(1, 2), xc.view(G * S, N // S, fin)).view(G, S, fout, fin).sum(1)
         else:
             dw = torch.bmm(dy.transpose(1, 2), x)
-        return dx, dw, dy.sum(1)
+        return dx, dw, dy.sum(1), None, None
 
 
 class _ReluL2Norm(torch.autograd.Function):

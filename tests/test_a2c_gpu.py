@@ -264,3 +264,26 @@ def test_fused_policy_equals_float64_policy_at_cfg4_size():
         assert err_f <= 2.0 * err_u + 1e-4, (name, err_f, err_u)
         checked += 1
     assert checked >= 16
+
+
+@pytest.mark.parametrize("G,N,fin,fout,relu", [(2, 7, 10, 33, True), (4, 1024, 100, 256, True), (3, 65, 32, 32, False)])
+def test_stacked_linear_epilogue_and_split_k_match_torch(G, N, fin, fout, relu):
+    """`_StackedLinear` with the in-place bias (+ relu) epilogue (swarm_bias_act, 128-bit and scalar paths) and the split-K
+    weight gradient against torch.baddbmm / F.relu autograd on the same float32 inputs."""
+    import torch.nn.functional as F
+    from swarm_b200.a2c import _StackedLinear
+    gen = torch.Generator(device="cuda").manual_seed(21)
+    mk = lambda *s: torch.randn(s, device="cuda", generator=gen)
+    x, w, b, gw = mk(G, N, fin), mk(G, fout, fin) * 0.1, mk(G, fout), mk(G, N, fout)
+    outs = []
+    for fused in (True, None):
+        xx, ww, bb = (t.clone().requires_grad_(True) for t in (x, w, b))
+        if fused:
+            y = _StackedLinear.apply(xx, ww, bb, relu, True)
+        else:
+            y = torch.baddbmm(bb.unsqueeze(1), xx, ww.transpose(1, 2))
+            y = F.relu(y) if relu else y
+        (y * gw).sum().backward()
+        outs.append((y.detach(), xx.grad, ww.grad, bb.grad))
+    for a, r in zip(*outs):
+        assert torch.allclose(a, r, rtol=1e-5, atol=1e-5 * max(1.0, float(r.abs().max())))
