@@ -440,6 +440,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
           TR(4);
           if (lane == 0) bulk_wait_read0();   // the previous bulk store has drained `stage` (long ago)
           __syncwarp();
+          TR(7);
           if (active) build_window<WC, OT>(p, cvt, lut4, sg, q, my_stage);
           fence_proxy_async();   // generic-proxy writes to `stage` ordered before the async-proxy read below
           __syncwarp();

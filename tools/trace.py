@@ -33,7 +33,7 @@ print("iteration rows; per warp: top->ready wait(cycles), compute ready->b4arr, 
 for it in range(10):
     if t[it, 0, 0] == 0: break
     w = t[it, :, 3] - t[it, :, 2]; c = t[it, :, 5] - t[it, :, 3]; tot = t[it, :, 6] - t[it, :, 0]
-    print(f"it{it}: start {t[it,:,0].min()-t0:7d}  prod(w0) {t[it,0,1]-t[it,0,0]:5d}  wait min/max {w.min():5d}/{w.max():5d}  compute min/max {c.min():5d}/{c.max():5d}  win {(t[it,:,5]-t[it,:,4]).mean():6.0f}  total {tot.mean():6.0f}")
+    print(f"it{it}: start {t[it,:,0].min()-t0:7d}  prod(w0) {t[it,0,1]-t[it,0,0]:5d}  wait min/max {w.min():5d}/{w.max():5d}  compute min/max {c.min():5d}/{c.max():5d}  win {(t[it,:,5]-t[it,:,4]).mean():6.0f} (stage drain wait {(t[it,:,7]-t[it,:,4]).mean():5.0f})  total {tot.mean():6.0f}")
 print("kernel span (cycles):", t[:, :, 6].max() - t0)
 cb = np.zeros(4096, np.uint64); L.swarm_debug_cta.argtypes = [C.c_void_p]; assert L.swarm_debug_cta(cb.ctypes.data) == 0
 smid = cb[3072:3072 + 444].astype(np.int64); waitc = cb[2048:2048 + 444].astype(np.int64); cb = cb.reshape(2048, 2)[:444].astype(np.int64); st = cb[:, 0] - cb[:, 0].min(); en = cb[:, 1] - cb[:, 0].min()
