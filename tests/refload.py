@@ -36,3 +36,27 @@ def export_state(env):
     g = np.array(env.grid, dtype=np.int8).T.copy()
     pos = np.array(env.n_drones_pos, dtype=np.float64).reshape(env.n_drones, 2)
     return g, pos, int(env.step_func_count)
+
+
+def ref_dql_namespace():
+    """{'AgentModel', 'Agent', ...} of the UNMODIFIED DQL_model/DQLearning.py.  The file is a script (argparse + the whole
+    training run at module level), so only its definitions — everything above the `env = DroneEnv(` line — are executed,
+    with `noVis_sim` resolved to the reference's own DQL env and an empty command line."""
+    import sys
+    if "DQLns" not in _cache:
+        path = os.path.join(REF_ROOT, "DQL_model", "DQLearning.py")
+        src = open(path).read()
+        head = src[:src.index("\nenv = DroneEnv(")]
+        saved_mod, saved_argv = sys.modules.get("noVis_sim"), sys.argv
+        sys.modules["noVis_sim"], sys.argv = ref_module("DQL"), ["DQLearning.py"]
+        try:
+            ns = {"__name__": "_ref_DQLearning"}
+            exec(compile(head, path, "exec"), ns)
+        finally:
+            sys.argv = saved_argv
+            if saved_mod is None:
+                del sys.modules["noVis_sim"]
+            else:
+                sys.modules["noVis_sim"] = saved_mod
+        _cache["DQLns"] = ns
+    return _cache["DQLns"]
