@@ -32,6 +32,7 @@ WORKLOADS = {
     "cfg5b": (1024, dict(row_count=256, col_count=256, n_drones=64, step_size=1.0, obs_mode="window", window=5)),
 }
 A2C_WORKLOAD = "cfg4_a2c"   # BASELINE configs[3]: the A2C/train.py rollout loop on the cfg4 env shape, env + policy end to end
+DQL_WORKLOAD = "cfg4_dql"   # the DQL_model/DQLearning.py loop (act + env step + memorise + replay) batched on the cfg4 env shape
 METRIC = "agent-steps/sec (device-timed)"
 UNIT = "agent-steps/s"
 
@@ -305,13 +306,117 @@ def run_a2c(args, rank, world, local):
     os._exit(0)
 
 
+def run_dql(args, rank, world, local):
+    """The batched re-expression of DQL_model/DQLearning.py: a bench "step" is ONE pass of its inner loop for all
+    envs — 8 stacked AgentModel nets act, fused env step (DQL reward), memorise, replay on a minibatch of 32 transitions per env
+    (the reference's --batch_size per env step) with one AdamW step.  value = N * D * steps / time, device-timed."""
+    n_envs, kw = WORKLOADS["cfg4"]
+    kw = dict(kw)
+    if args.envs:
+        n_envs = args.envs
+    if args.impl == "reference":
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "metric": "agent-steps/sec (env+agent, deep-Q loop)", "config": {"workload": DQL_WORKLOAD},
+                              "unavailable": "the reference DQLearning.py is pure Python/PyTorch under /root/reference and cannot travel to the GPU box; "
+                                             "measured in the build container: 15.9 agent-steps/s (8 cores, 10x10, 8 drones; profiles/r1_dql_reference_cpu.json)"}))
+        return
+    quiet_stdout()
+    import torch
+    import torch.distributed as dist
+    from swarm_b200 import BatchedDroneEnv
+    from swarm_b200.dql import BatchedDQLAgent
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl ours) needs a B200; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cuda.matmul.allow_tf32 = bool(args.tf32)
+    D = kw["n_drones"]
+    K = args.steps if args.steps != 1024 else 50
+    W = max(args.warmup if args.warmup != 10 else 40, 40)      # the memory must pass batch_size (33 steps) before replay runs
+    env = BatchedDroneEnv(n_envs, reward_mode="DQL", auto_reset=True, seed=2026, env_id_base=rank * n_envs, **kw)
+    torch.manual_seed(1234)                                  # identical initial weights on every rank
+    agent = BatchedDQLAgent(env, memory_steps=48, batch_size=32 * n_envs, seed=99 + rank)
+    for _ in range(W):
+        agent.train_step()
+    torch.cuda.synchronize(dev)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = env.launch_count
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(K):
+        agent.train_step()
+    t1.record()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = t0.elapsed_time(t1)
+    env_launches = env.launch_count - l0
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    for _ in range(K):                                       # e2e: the loss read back to the host every step
+        float(agent.train_step()[2].item())
+    torch.cuda.synchronize(dev)
+    e2e_ms = (time.perf_counter() - w0) * 1e3
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = (float(x) for x in t.tolist())
+    if rank == 0:
+        S = kw["row_count"] * kw["col_count"]
+        macs = S * 64 + 2 * D * 64 + 128 * 64 + 64 * 32 + 32 * 4                                      # one AgentModel
+        B = agent.batch_size
+        flops_step = 2.0 * macs * D * (n_envs + 4 * B)         # act forward on N rows; replay: Q(s) fwd + 2x bwd, Q(s') fwd on B rows
+        agent_steps = float(n_envs) * D * K * world
+        try:
+            peak = float(json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]); src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+        except Exception:
+            peak, src = 1500.0, "fallback (B200_PROFILING.md)"
+        ach = flops_step * K / (ms * 1e-3) / 1e12
+        line = {
+            "metric": "agent-steps/sec (env+agent, deep-Q loop, device-timed)", "value": agent_steps / (ms * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "tf32 GEMMs" if args.tf32 else "f32 (GEMMs via cuBLAS, as the reference's float32)", "data": "synthetic",
+            "config": {"workload": DQL_WORKLOAD, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw, "reward_mode": "DQL",
+                       "agent": "DQL_model/DQLearning.py AgentModel x 8 drones (random init), AdamW lr 1e-4, gamma 0.95, epsilon from 1.0 decaying 0.995 per replay",
+                       "replay_batch": B, "memory_steps": agent.K,
+                       "step": "act (epsilon-greedy) + env step + memorise + replay (targets, loss, backward, one AdamW step)",
+                       "l2": "replay activations [8, 524288, 128] float32 = 2 GB per layer, far beyond the 126 MB L2",
+                       "parallelism": f"data-parallel x{world}: envs sharded, one gradient all-reduce per replay" if world > 1 else "single GPU"},
+            "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None, "peak_source": src,
+                         "kernel": "cuBLAS SGEMM + element-wise torch kernels (library code: this row is a caller of the hot path, not the hot path)",
+                         "algorithmic_flops_per_step": flops_step},
+            "e2e": {"value": agent_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4, "steps": K,
+                    "ms_per_step": e2e_ms / K, "api": "BatchedDQLAgent.train_step() + loss.item()"},
+            "gpu_launches": int(env_launches), "gpu_launches_note": "swarm_step + the masked swarm_reset (step cap, also the state copy) per step; torch/cuBLAS kernels not counted",
+            "clocks": clocks,
+            "cpu_baseline": {"value": 15.9, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified DQLearning.py Agent + env loop, 60 env-steps with replay(32), 10x10, 8 drones, measured in the build container by tools/dql_ref_cpu.py (cannot travel to the GPU box)"},
+        }
+        emit(line)
+    sys.stdout.flush()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    env.close()
+    sys.stdout.flush(); sys.stderr.flush()
+    os._exit(0)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=1024)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + [A2C_WORKLOAD])
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + [A2C_WORKLOAD, DQL_WORKLOAD])
     ap.add_argument("--rollout-steps", type=int, default=25, help="cfg4_a2c: env steps per outer iteration (A2C/main.py default)")
     ap.add_argument("--tf32", action="store_true", help="cfg4_a2c: allow TF32 tensor-core GEMMs for the policy (default: fp32, as the reference)")
     ap.add_argument("--obs-dtype", default="float32", choices=["float32", "uint8"],
@@ -332,6 +437,8 @@ def main():
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     if args.workload == A2C_WORKLOAD:
         return run_a2c(args, rank, world, local)
+    if args.workload == DQL_WORKLOAD:
+        return run_dql(args, rank, world, local)
     n_envs, kw = WORKLOADS[args.workload]
     kw = dict(kw)
     if args.envs:

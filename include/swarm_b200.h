@@ -200,10 +200,12 @@ int swarm_gru_gates_fwd(const float* gi, const float* bias_hh, int64_t n_envs, i
 int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const float* dh, int64_t n_envs,
                         int32_t n_nets, int32_t hidden, float* dgi_out, float* dnr_out, void* stream);
 
-/* Epilogue of the stacked linears (nn.Linear bias + F.relu, A2C/models.py:106-116) after a plain batched GEMM, in place:
- *   y[g][n][:] = act(y[g][n][:] + bias[g][:])      y float32 [G][N][F], bias float32 [G][F], relu != 0 applies max(., 0). */
+/* Epilogue of the stacked linears (nn.Linear bias + F.relu, A2C/models.py:106-116; bias + torch.tanh of the deep-Q nets,
+ * DQL_model/DQLearning.py:43-48) after a plain batched GEMM, in place:
+ *   y[g][n][:] = act(y[g][n][:] + bias[g][:])      y float32 [G][N][F], bias float32 [G][F]
+ * act: 0 identity, 1 max(., 0), 2 tanhf; anything else is SWARM_ERR_INVALID_ARG. */
 int swarm_bias_act(float* y, const float* bias, int32_t n_nets, int64_t n_rows, int32_t features,
-                   int32_t relu, void* stream);
+                   int32_t act, void* stream);
 /* relu + F.normalize(dim=-1) of the policy's state embedding (A2C/models.py:107-108) in one pass:
  *   y = max(x, 0), out = y / max(||y||_2, eps)      x, out float32 [rows][features], 16 B aligned. */
 int swarm_relu_l2norm_fwd(const float* x, int64_t rows, int32_t features, float eps, float* out,

@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(256) gru_gates_bwd_kernel(const float* __restr
 // y[g][n][:] += bias[g][:], optionally followed by relu, in place: the epilogue of the stacked linears (nn.Linear + F.relu of
 // A2C/models.py:106-116) after a plain batched GEMM — one read and one write of y instead of a broadcast-bias fill, the
 // GEMM's read of it, and a separate relu pass.
-__global__ void __launch_bounds__(256) bias_act_kernel(float* __restrict__ y, const float* __restrict__ bias, int G, long long N, int F, int relu) {
+__global__ void __launch_bounds__(256) bias_act_kernel(float* __restrict__ y, const float* __restrict__ bias, int G, long long N, int F, int act) {
   if ((F & 3) == 0) {
     const int F4 = F >> 2;
     const long long per_net = N * F4, total = per_net * G;
@@ -204,7 +204,8 @@ __global__ void __launch_bounds__(256) bias_act_kernel(float* __restrict__ y, co
       float4 v = reinterpret_cast<float4*>(y)[i];
       const float4 b = __ldg(reinterpret_cast<const float4*>(bias + (size_t)g * F + f));
       v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-      if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+      if (act == 1) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+      else if (act == 2) { v.x = tanhf(v.x); v.y = tanhf(v.y); v.z = tanhf(v.z); v.w = tanhf(v.w); }
       reinterpret_cast<float4*>(y)[i] = v;
     }
     return;
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(256) bias_act_kernel(float* __restrict__ y, co
   const long long per_net = N * F, total = per_net * G;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const float v = y[i] + __ldg(bias + (size_t)(i / per_net) * F + (i % F));
-    y[i] = relu ? fmaxf(v, 0.f) : v;
+    y[i] = act == 1 ? fmaxf(v, 0.f) : (act == 2 ? tanhf(v) : v);
   }
 }
 

@@ -598,8 +598,8 @@ extern "C" int swarm_gru_gates_bwd(const float* gi, const float* bias_hh, const 
   return SWARM_OK;
 }
 
-extern "C" int swarm_bias_act(float* y, const float* bias, int32_t n_nets, int64_t n_rows, int32_t features, int32_t relu, void* stream) {
-  if (!y || !bias || n_nets < 1 || n_rows < 1 || features < 1) return SWARM_ERR_INVALID_ARG;
+extern "C" int swarm_bias_act(float* y, const float* bias, int32_t n_nets, int64_t n_rows, int32_t features, int32_t act, void* stream) {
+  if (!y || !bias || n_nets < 1 || n_rows < 1 || features < 1 || act < 0 || act > 2) return SWARM_ERR_INVALID_ARG;
   if ((features & 3) == 0 && (((uintptr_t)y | (uintptr_t)bias) & 15)) return SWARM_ERR_INVALID_ARG;   // 128-bit path
   int sms = 0;
   int rc = current_sm_count(&sms);
@@ -607,7 +607,7 @@ extern "C" int swarm_bias_act(float* y, const float* bias, int32_t n_nets, int64
   const long long work = (long long)n_nets * n_rows * ((features & 3) == 0 ? features / 4 : features);
   long long b = (work + 255) / 256;
   if (b > (long long)sms * 16) b = (long long)sms * 16;
-  bias_act_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(y, bias, n_nets, n_rows, features, relu);
+  bias_act_kernel<<<(int)b, 256, 0, (cudaStream_t)stream>>>(y, bias, n_nets, n_rows, features, act);
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;
 }

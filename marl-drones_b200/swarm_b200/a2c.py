@@ -257,17 +257,21 @@ class _StackedLinear(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, b, relu=False, fused=True):
+        """relu: False / 0 none, True / 1 relu, 2 tanh (the deep-Q nets, DQL_model/DQLearning.py:43-48)."""
         G, N, _ = x.shape
+        act = int(relu)
         if fused and x.is_cuda and x.dtype == torch.float32:
-            y = torch.bmm(x, w.transpose(1, 2))                             # plain GEMM, then bias (+ relu) in one in-place pass
-            check(_lib.lib().swarm_bias_act(y.data_ptr(), b.detach().contiguous().data_ptr(), G, N, y.shape[2], int(relu),
+            y = torch.bmm(x, w.transpose(1, 2))                             # plain GEMM, then bias (+ activation) in one in-place pass
+            check(_lib.lib().swarm_bias_act(y.data_ptr(), b.detach().contiguous().data_ptr(), G, N, y.shape[2], act,
                                             _raw_stream(x.device.index)))
         else:
             y = torch.baddbmm(b.unsqueeze(1), x, w.transpose(1, 2))
-            if relu:
+            if act == 1:
                 y = F.relu(y)
-        ctx.relu = relu
-        ctx.save_for_backward(x, w, y if relu else None)
+            elif act == 2:
+                y = torch.tanh(y)
+        ctx.act = act
+        ctx.save_for_backward(x, w, y if act else None)
         return y
 
     @staticmethod
@@ -276,8 +280,10 @@ class _StackedLinear(torch.autograd.Function):
         G, N, fin = x.shape
         fout = w.shape[1]
         dy = dy.contiguous()
-        if ctx.relu:
+        if ctx.act == 1:
             dy = torch.ops.aten.threshold_backward(dy, y, 0)               # relu'(pre) = [y > 0]
+        elif ctx.act == 2:
+            dy = torch.ops.aten.tanh_backward(dy, y)                        # tanh'(pre) = 1 - y^2
         dx = torch.bmm(dy, w) if ctx.needs_input_grad[0] else None
         S = 1
         while S < 16 and N % (2 * S) == 0 and N // (2 * S) >= 512:

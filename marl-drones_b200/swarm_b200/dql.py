@@ -68,8 +68,11 @@ class BatchedQNet(nn.Module):
         return {f"{name}.{kind}": getattr(self, f"{name}__{kind}")[i].detach().clone()
                 for name, _, _ in _q_shapes(self.state_size, self.n_drones, self.action_size) for kind in ("weight", "bias")}
 
-    def _lin(self, x, name):
-        return torch.baddbmm(getattr(self, f"{name}__bias").unsqueeze(1), x, getattr(self, f"{name}__weight").transpose(1, 2))
+    fused = True   # float32 CUDA tensors: plain batched GEMM + swarm_bias_act (bias + tanh in place) and split-K weight gradients
+
+    def _lin(self, x, name, act=0):
+        from .a2c import _StackedLinear
+        return _StackedLinear.apply(x, getattr(self, f"{name}__weight"), getattr(self, f"{name}__bias"), act, bool(self.fused))
 
     def _lin_shared(self, x, name):
         w, b = getattr(self, f"{name}__weight"), getattr(self, f"{name}__bias")
@@ -90,8 +93,8 @@ class BatchedQNet(nn.Module):
         # the two input layers see the same rows in every net: ONE [N, in] x [in, D*64] product each instead of D
         out = torch.cat([self._lin_shared(s, "state_input"), self._lin_shared(p, "drone_input")], dim=-1).tanh_()
         out = F.normalize(out, dim=-1)                                      # :46 (L2 over features, eps 1e-12)
-        out = torch.tanh(self._lin(out, "dense1"))
-        out = torch.tanh(self._lin(out, "dense2"))
+        out = self._lin(out, "dense1", 2)                                   # :47-48 torch.tanh(dense(.))
+        out = self._lin(out, "dense2", 2)
         return self._lin(out, "dense3")
 
 
@@ -123,7 +126,7 @@ class BatchedDQLAgent:
     replace `deque(maxlen=3000)`; `batch_size` transitions are drawn without replacement (`random.sample`)."""
 
     def __init__(self, env, net=None, gamma=0.95, epsilon=1.0, epsilon_min=0.01, epsilon_decay=0.995, lr=1e-4,
-                 memory_steps=64, batch_size=None, max_steps=2000, terminal_reward=1000.0, seed=0):
+                 memory_steps=64, batch_size=None, max_steps=2000, terminal_reward=1000.0, seed=0, group=None):
         self.env, self.N, self.D = env, env.num_envs, env.n_drones
         dev = env.device
         self.net = net if net is not None else BatchedQNet(env.state_size, env.n_drones, env.action_size, device=dev)
@@ -132,6 +135,7 @@ class BatchedDQLAgent:
         self.K = memory_steps
         self.batch_size = batch_size if batch_size is not None else 32 * self.N                       # 32 per env (:14)
         self.max_steps, self.terminal_reward = max_steps, terminal_reward
+        self.group = group              # torch.distributed group of data-parallel replicas (envs sharded over ranks)
         self.gen = torch.Generator(device=dev)
         self.gen.manual_seed(seed)
         S, N, D, K = env.state_size, self.N, self.D, self.K
@@ -196,10 +200,27 @@ class BatchedDQLAgent:
         loss = dql_loss(self.net, state, pos, act, rew, nstate, npos, done, self.gamma)
         self.opt.zero_grad(set_to_none=True)
         loss.backward()
+        self.allreduce_grads_()
         self.opt.step()
         if self.epsilon > self.epsilon_min:
             self.epsilon *= self.epsilon_decay
         return loss.detach()
+
+    @torch.no_grad()
+    def allreduce_grads_(self):
+        """Data-parallel replicas: ONE all-reduce of the flattened gradient per replay, so every rank steps along the mean
+        over all ranks' minibatches (same scheme as A2CTrainer.allreduce_grads_)."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+            return
+        grads = [p.grad for p in self.net.parameters() if p.grad is not None]
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat, group=self.group)
+        flat.div_(dist.get_world_size(self.group))
+        off = 0
+        for g in grads:
+            g.copy_(flat[off:off + g.numel()].view_as(g))
+            off += g.numel()
 
     def train_step(self):
         """One iteration of the reference's inner loop: step, then `if len(memory) > batch_size: replay` (:186-187)."""

@@ -266,9 +266,10 @@ def test_fused_policy_equals_float64_policy_at_cfg4_size():
     assert checked >= 16
 
 
-@pytest.mark.parametrize("G,N,fin,fout,relu", [(2, 7, 10, 33, True), (4, 1024, 100, 256, True), (3, 65, 32, 32, False)])
+@pytest.mark.parametrize("G,N,fin,fout,relu", [(2, 7, 10, 33, True), (4, 1024, 100, 256, True), (3, 65, 32, 32, False),
+                                               (8, 2048, 128, 64, 2), (3, 9, 5, 7, 2)])
 def test_stacked_linear_epilogue_and_split_k_match_torch(G, N, fin, fout, relu):
-    """`_StackedLinear` with the in-place bias (+ relu) epilogue (swarm_bias_act, 128-bit and scalar paths) and the split-K
+    """`_StackedLinear` with the in-place bias (+ relu, or tanh when relu == 2: the deep-Q nets) epilogue (swarm_bias_act, 128-bit and scalar paths) and the split-K
     weight gradient against torch.baddbmm / F.relu autograd on the same float32 inputs."""
     import torch.nn.functional as F
     from swarm_b200.a2c import _StackedLinear
@@ -282,7 +283,7 @@ def test_stacked_linear_epilogue_and_split_k_match_torch(G, N, fin, fout, relu):
             y = _StackedLinear.apply(xx, ww, bb, relu, True)
         else:
             y = torch.baddbmm(bb.unsqueeze(1), xx, ww.transpose(1, 2))
-            y = F.relu(y) if relu else y
+            y = torch.tanh(y) if relu == 2 else (F.relu(y) if relu else y)
         (y * gw).sum().backward()
         outs.append((y.detach(), xx.grad, ww.grad, bb.grad))
     for a, r in zip(*outs):
