@@ -215,6 +215,17 @@ int swarm_relu_l2norm_fwd(const float* x, int64_t rows, int32_t features, float 
 int swarm_relu_l2norm_bwd(const float* x, const float* grad_out, int64_t rows, int32_t features,
                           float eps, float* grad_x, void* stream);
 
+/* Embedding of the stacked deep-Q nets (DQL_model/DQLearning.py:43-46) in one pass:
+ *   out[d][n][:] = F.normalize(cat(tanh(a[n][d][:]), tanh(b[n][d][:])))      (L2 over the fa + fb features, clamp eps)
+ * a float32 [n_rows][n_nets][fa] = state_input(state) and b float32 [n_rows][n_nets][fb] = drone_input(drone_pos) of all nets
+ * (bias included), out float32 [n_nets][n_rows][fa + fb].  fa, fb multiples of 4, fa + fb <= 256, 16 B aligned pointers. */
+int swarm_embed_tanh_l2norm_fwd(const float* a, const float* b, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb,
+                                float eps, float* out, void* stream);
+/* Its backward: grad_out float32 [n_nets][n_rows][fa + fb] -> grad_a [n_rows][n_nets][fa], grad_b [n_rows][n_nets][fb]
+ * (tanh recomputed from a, b). */
+int swarm_embed_tanh_l2norm_bwd(const float* a, const float* b, const float* grad_out, int64_t n_rows, int32_t n_nets,
+                                int32_t fa, int32_t fb, float eps, float* grad_a, float* grad_b, void* stream);
+
 /* -- the path's one collective: episode statistics over NCCL --------------------- */
 /* libnccl.so.2 is bound with dlopen at first use (the process's own copy, e.g. PyTorch's); no link-time dependency.
  * `comm` is an ncclComm_t passed as void*: either one the caller already owns, or one made here:

@@ -298,4 +298,85 @@ __global__ void __launch_bounds__(256) relu_l2norm_bwd_kernel(const float* __res
   }
 }
 
+// The deep-Q nets' embedding (DQL_model/DQLearning.py:43-46): out = F.normalize(cat(tanh(state_input(s)), tanh(drone_input(p))))
+// for all stacked nets in one pass.  a float32 [N][D][fa], b float32 [N][D][fb] are the two shared input-layer products (bias
+// included), out float32 [D][N][fa + fb] is the layout the stacked dense layers consume.  One warp per (env row, net);
+// fa, fb multiples of 4, fa + fb <= 256 (tanh values stay in registers between the norm and the store).
+__device__ __forceinline__ float4 ld_cat4(const float* ar, const float* br, int fa, int k) {
+  return k < fa ? *reinterpret_cast<const float4*>(ar + k) : *reinterpret_cast<const float4*>(br + (k - fa));
+}
+
+__global__ void __launch_bounds__(256) embed_tanh_l2norm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b, long long N, int D, int fa, int fb,
+                                                                    float eps, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31, F = fa + fb;
+  const long long rows = N * D;
+  const long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w0; r < rows; r += nw) {
+    const float* ar = a + (size_t)r * fa;
+    const float* br = b + (size_t)r * fb;
+    float* orow = out + ((size_t)(r % D) * N + (size_t)(r / D)) * F;
+    float4 y[2];
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int k = lane * 4 + j * 128;
+      if (k < F) {
+        const float4 v = ld_cat4(ar, br, fa, k);
+        y[j] = make_float4(tanhf(v.x), tanhf(v.y), tanhf(v.z), tanhf(v.w));
+        ss += y[j].x * y[j].x + y[j].y * y[j].y + y[j].z * y[j].z + y[j].w * y[j].w;
+      }
+    }
+    const float inv = 1.0f / fmaxf(sqrtf(warp_sum(ss)), eps);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int k = lane * 4 + j * 128;
+      if (k < F) *reinterpret_cast<float4*>(orow + k) = make_float4(y[j].x * inv, y[j].y * inv, y[j].z * inv, y[j].w * inv);
+    }
+  }
+}
+
+// Backward: y = tanh(pre) recomputed, d = max(||y||, eps), g = d loss / d out [D][N][F]:
+//   dy = g / d - y * (g . y) / d^3 (second term only when ||y|| > eps);   dpre = dy * (1 - y^2)  ->  da [N][D][fa], db [N][D][fb]
+__global__ void __launch_bounds__(256) embed_tanh_l2norm_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ g,
+                                                                    long long N, int D, int fa, int fb, float eps, float* __restrict__ da, float* __restrict__ db) {
+  const int lane = threadIdx.x & 31, F = fa + fb;
+  const long long rows = N * D;
+  const long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w0; r < rows; r += nw) {
+    const float* ar = a + (size_t)r * fa;
+    const float* br = b + (size_t)r * fb;
+    const float* gr = g + ((size_t)(r % D) * N + (size_t)(r / D)) * F;
+    float4 y[2], u[2];
+    float ss = 0.f, gy = 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int k = lane * 4 + j * 128;
+      if (k < F) {
+        const float4 v = ld_cat4(ar, br, fa, k);
+        u[j] = *reinterpret_cast<const float4*>(gr + k);
+        y[j] = make_float4(tanhf(v.x), tanhf(v.y), tanhf(v.z), tanhf(v.w));
+        ss += y[j].x * y[j].x + y[j].y * y[j].y + y[j].z * y[j].z + y[j].w * y[j].w;
+        gy += u[j].x * y[j].x + u[j].y * y[j].y + u[j].z * y[j].z + u[j].w * y[j].w;
+      }
+    }
+    const float nrm = sqrtf(warp_sum(ss));
+    gy = warp_sum(gy);
+    const float d = fmaxf(nrm, eps), inv = 1.0f / d;
+    const float c3 = nrm > eps ? gy * inv * inv * inv : 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int k = lane * 4 + j * 128;
+      if (k < F) {
+        float4 t;
+        t.x = (u[j].x * inv - y[j].x * c3) * (1.f - y[j].x * y[j].x);
+        t.y = (u[j].y * inv - y[j].y * c3) * (1.f - y[j].y * y[j].y);
+        t.z = (u[j].z * inv - y[j].z * c3) * (1.f - y[j].z * y[j].z);
+        t.w = (u[j].w * inv - y[j].w * c3) * (1.f - y[j].w * y[j].w);
+        float* dst = k < fa ? da + (size_t)r * fa + k : db + (size_t)r * fb + (k - fa);
+        *reinterpret_cast<float4*>(dst) = t;
+      }
+    }
+  }
+}
+
 }  // namespace swarm

@@ -642,6 +642,32 @@ extern "C" int swarm_relu_l2norm_bwd(const float* x, const float* grad_out, int6
   return SWARM_OK;
 }
 
+extern "C" int swarm_embed_tanh_l2norm_fwd(const float* a, const float* b, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb, float eps, float* out,
+                                           void* stream) {
+  if (!a || !b || !out || n_rows < 1 || n_nets < 1 || fa < 4 || fb < 4 || (fa & 3) || (fb & 3) || fa + fb > 256 ||
+      (((uintptr_t)a | (uintptr_t)b | (uintptr_t)out) & 15))
+    return SWARM_ERR_INVALID_ARG;
+  int blocks = 0;
+  int rc = row_kernel_blocks(n_rows * n_nets, &blocks);
+  if (rc) return rc;
+  embed_tanh_l2norm_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, b, n_rows, n_nets, fa, fb, eps, out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_embed_tanh_l2norm_bwd(const float* a, const float* b, const float* grad_out, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb,
+                                           float eps, float* grad_a, float* grad_b, void* stream) {
+  if (!a || !b || !grad_out || !grad_a || !grad_b || n_rows < 1 || n_nets < 1 || fa < 4 || fb < 4 || (fa & 3) || (fb & 3) || fa + fb > 256 ||
+      (((uintptr_t)a | (uintptr_t)b | (uintptr_t)grad_out | (uintptr_t)grad_a | (uintptr_t)grad_b) & 15))
+    return SWARM_ERR_INVALID_ARG;
+  int blocks = 0;
+  int rc = row_kernel_blocks(n_rows * n_nets, &blocks);
+  if (rc) return rc;
+  embed_tanh_l2norm_bwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, b, grad_out, n_rows, n_nets, fa, fb, eps, grad_a, grad_b);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ NCCL (statistics only)
 // The path's one collective: ncclAllReduce(SUM, int64[8]) of the episode statistics, 64 B per rank.  libnccl is
 // bound at run time (dlopen of the copy the process already carries — PyTorch's — else the system one), so the library has no

@@ -35,6 +35,36 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+class _EmbedTanhL2Norm(torch.autograd.Function):
+    """F.normalize(cat(tanh(a), tanh(b)), dim=-1) for the stacked nets (DQLearning.py:43-46) in one pass each way:
+    a [N, D, fa], b [N, D, fb] float32 CUDA (the shared input-layer products) -> [D, N, fa + fb]
+    (swarm_embed_tanh_l2norm_fwd / _bwd)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        from . import _lib
+        a, b = a.contiguous(), b.contiguous()
+        N, D, fa = a.shape
+        fb = b.shape[2]
+        out = torch.empty((D, N, fa + fb), dtype=torch.float32, device=a.device)
+        _lib.check(_lib.lib().swarm_embed_tanh_l2norm_fwd(a.data_ptr(), b.data_ptr(), N, D, fa, fb, 1e-12, out.data_ptr(),
+                                                          torch._C._cuda_getCurrentRawStream(a.device.index)))
+        ctx.save_for_backward(a, b)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import _lib
+        a, b = ctx.saved_tensors
+        N, D, fa = a.shape
+        fb = b.shape[2]
+        g = g.contiguous()
+        da, db = torch.empty_like(a), torch.empty_like(b)
+        _lib.check(_lib.lib().swarm_embed_tanh_l2norm_bwd(a.data_ptr(), b.data_ptr(), g.data_ptr(), N, D, fa, fb, 1e-12, da.data_ptr(),
+                                                          db.data_ptr(), torch._C._cuda_getCurrentRawStream(a.device.index)))
+        return da, db
+
+
 # (name in AgentModel, in_features, out_features); S = state_size, D = n_drones, A = action_size   (DQLearning.py:30-34)
 def _q_shapes(S, D, A):
     return (("state_input", S, 64), ("drone_input", 2 * D, 64), ("dense1", 128, 64), ("dense2", 64, 32), ("dense3", 32, A))
@@ -75,9 +105,10 @@ class BatchedQNet(nn.Module):
         return _StackedLinear.apply(x, getattr(self, f"{name}__weight"), getattr(self, f"{name}__bias"), act, bool(self.fused))
 
     def _lin_shared(self, x, name):
+        """-> [N, D, out]: the layer of every net applied to the same rows."""
         w, b = getattr(self, f"{name}__weight"), getattr(self, f"{name}__bias")
         D, fo, fi = w.shape
-        return torch.addmm(b.reshape(1, D * fo), x, w.reshape(D * fo, fi).t()).view(x.shape[0], D, fo).transpose(0, 1)
+        return torch.addmm(b.reshape(1, D * fo), x, w.reshape(D * fo, fi).t()).view(x.shape[0], D, fo)
 
     def forward(self, state, drone_pos):
         """state [N, S] (any real dtype), drone_pos [N, D, 2] -> Q [D, N, A]; row n of net i equals
@@ -91,8 +122,11 @@ class BatchedQNet(nn.Module):
         s = (s - mu) / std
         p = drone_pos.reshape(N, 2 * D).to(dt)
         # the two input layers see the same rows in every net: ONE [N, in] x [in, D*64] product each instead of D
-        out = torch.cat([self._lin_shared(s, "state_input"), self._lin_shared(p, "drone_input")], dim=-1).tanh_()
-        out = F.normalize(out, dim=-1)                                      # :46 (L2 over features, eps 1e-12)
+        ea, eb = self._lin_shared(s, "state_input"), self._lin_shared(p, "drone_input")
+        if self.fused and ea.is_cuda and ea.dtype == torch.float32:
+            out = _EmbedTanhL2Norm.apply(ea, eb)                            # tanh + cat + F.normalize + [N, D] -> [D, N] in one pass
+        else:
+            out = F.normalize(torch.cat([ea, eb], dim=-1).transpose(0, 1).tanh(), dim=-1)   # :43-46 (L2 over features, eps 1e-12)
         out = self._lin(out, "dense1", 2)                                   # :47-48 torch.tanh(dense(.))
         out = self._lin(out, "dense2", 2)
         return self._lin(out, "dense3")

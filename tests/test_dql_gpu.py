@@ -101,3 +101,52 @@ def test_train_step_replays_and_learns():
         opt.step()
     assert float(l.detach()) < first
     env.close()
+
+
+@pytest.mark.parametrize("N,D,fa,fb", [(1000, 8, 64, 64), (37, 3, 64, 64), (5, 2, 8, 4), (64, 4, 128, 128)])
+def test_fused_embedding_matches_torch(N, D, fa, fb):
+    """swarm_embed_tanh_l2norm_fwd / _bwd against F.normalize(cat(tanh, tanh)) autograd on the same float32 inputs, with
+    float64 as the yardstick (DQLearning.py:43-46); includes an all-zero row (norm below eps)."""
+    import torch.nn.functional as F
+    from swarm_b200.dql import _EmbedTanhL2Norm
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    a = torch.randn((N, D, fa), device="cuda", generator=gen) * 2
+    b = torch.randn((N, D, fb), device="cuda", generator=gen) * 2
+    a[0, 0], b[0, 0] = 0.0, 0.0
+    gw = torch.randn((D, N, fa + fb), device="cuda", generator=gen)
+    ref = lambda x, y: F.normalize(torch.cat([x, y], dim=-1).transpose(0, 1).tanh(), dim=-1)   # noqa: E731
+    res = []
+    for fn, dt in ((_EmbedTanhL2Norm.apply, torch.float32), (ref, torch.float32), (ref, torch.float64)):
+        aa, bb = (t.to(dt).clone().requires_grad_(True) for t in (a, b))
+        o = fn(aa, bb)
+        (o * gw.to(dt)).sum().backward()
+        res.append((o.detach().double(), aa.grad.double(), bb.grad.double()))
+    for got, t32, t64 in zip(*res):
+        scale = max(1.0, float(t64.abs().max()))
+        err_f, err_t = float((got - t64).abs().max()) / scale, float((t32 - t64).abs().max()) / scale
+        assert err_f <= 2.0 * err_t + 2e-6, (err_f, err_t)
+    assert torch.equal(res[0][0][0, 0], torch.zeros(fa + fb, dtype=torch.float64, device="cuda"))
+
+
+def test_fused_qnet_equals_unfused():
+    from swarm_b200.dql import BatchedQNet, dql_loss
+    torch.manual_seed(0)
+    net = BatchedQNet(100, 8, device="cuda")
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    B = 4096
+    state = torch.randint(0, 2, (B, 100), device="cuda", generator=gen).float()
+    nstate = state * (torch.rand((B, 100), device="cuda", generator=gen) > 0.05)
+    pos = torch.randint(0, 10, (B, 8, 2), device="cuda", generator=gen).float()
+    act = torch.randint(0, 3, (B, 8), device="cuda", generator=gen, dtype=torch.uint8)
+    rew = torch.randint(-1, 32, (B,), device="cuda", generator=gen).float()
+    done = torch.rand(B, device="cuda", generator=gen) < 0.05
+    outs = []
+    for fused in (True, False):
+        net.fused = fused
+        net.zero_grad(set_to_none=True)
+        q = net(state, pos)
+        loss = dql_loss(net, state, pos, act, rew, nstate, pos, done, 0.95)
+        loss.backward()
+        outs.append([q.detach(), loss.detach()] + [p.grad.clone() for p in net.parameters()])
+    for a, r in zip(*outs):
+        torch.testing.assert_close(a, r, rtol=2e-4, atol=2e-5 * max(1.0, float(r.abs().max())))
