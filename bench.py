@@ -396,7 +396,7 @@ def run_dql(args, rank, world, local):
                          "algorithmic_flops_per_step": flops_step},
             "e2e": {"value": agent_steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4, "steps": K,
                     "ms_per_step": e2e_ms / K, "api": "BatchedDQLAgent.train_step() + loss.item()"},
-            "gpu_launches": int(env_launches + K * 13), "gpu_launches_note": "per step: swarm_step + the masked swarm_reset (step cap, also the state copy); swarm_embed_tanh_l2norm_fwd + 3 swarm_bias_act per net pass (act, Q(s), Q(s')) and one swarm_embed_tanh_l2norm_bwd; torch/cuBLAS kernels not counted",
+            "gpu_launches": int(env_launches + K * 16), "gpu_launches_note": "per step: swarm_step + the masked swarm_reset (step cap, also the state copy); swarm_row_standardize + swarm_embed_tanh_l2norm_fwd + 3 swarm_bias_act per net pass (act, Q(s), Q(s')) and one swarm_embed_tanh_l2norm_bwd; torch/cuBLAS kernels not counted",
             "clocks": clocks,
             "cpu_baseline": {"value": 15.9, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified DQLearning.py Agent + env loop, 60 env-steps with replay(32), 10x10, 8 drones, measured in the build container by tools/dql_ref_cpu.py (cannot travel to the GPU box)"},
         }

@@ -215,15 +215,21 @@ int swarm_relu_l2norm_fwd(const float* x, int64_t rows, int32_t features, float 
 int swarm_relu_l2norm_bwd(const float* x, const float* grad_out, int64_t rows, int32_t features,
                           float eps, float* grad_x, void* stream);
 
+/* Input normalisation of both policy families at batch 1 (A2C/models.py:101-103, DQL_model/DQLearning.py:40-42), row-wise:
+ *   out[r][:] = (x[r][:] - mean(x[r])) / std(x[r])      unbiased std (torch.Tensor.std()); x, out float32 [rows][features]. */
+int swarm_row_standardize(const float* x, int64_t rows, int32_t features, float* out, void* stream);
+
 /* Embedding of the stacked deep-Q nets (DQL_model/DQLearning.py:43-46) in one pass:
- *   out[d][n][:] = F.normalize(cat(tanh(a[n][d][:]), tanh(b[n][d][:])))      (L2 over the fa + fb features, clamp eps)
- * a float32 [n_rows][n_nets][fa] = state_input(state) and b float32 [n_rows][n_nets][fb] = drone_input(drone_pos) of all nets
- * (bias included), out float32 [n_nets][n_rows][fa + fb].  fa, fb multiples of 4, fa + fb <= 256, 16 B aligned pointers. */
-int swarm_embed_tanh_l2norm_fwd(const float* a, const float* b, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb,
+ *   out[d][n][:] = F.normalize(cat(tanh(a[n][d][:] + bias_a[d][:]), tanh(b[n][d][:] + bias_b[d][:])))   (L2 over fa + fb, clamp eps)
+ * a float32 [n_rows][n_nets][fa] = state_input's product with the state rows and b float32 [n_rows][n_nets][fb] = drone_input's
+ * with the drone positions, for all nets; bias_a [n_nets][fa], bias_b [n_nets][fb] may be NULL (bias already added);
+ * out float32 [n_nets][n_rows][fa + fb].  fa, fb multiples of 4, fa + fb <= 256, 16 B aligned pointers. */
+int swarm_embed_tanh_l2norm_fwd(const float* a, const float* b, const float* bias_a, const float* bias_b, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb,
                                 float eps, float* out, void* stream);
 /* Its backward: grad_out float32 [n_nets][n_rows][fa + fb] -> grad_a [n_rows][n_nets][fa], grad_b [n_rows][n_nets][fb]
- * (tanh recomputed from a, b). */
-int swarm_embed_tanh_l2norm_bwd(const float* a, const float* b, const float* grad_out, int64_t n_rows, int32_t n_nets,
+ * (tanh recomputed from a, b and the biases; the bias gradients are the column sums of grad_a / grad_b over n_rows). */
+int swarm_embed_tanh_l2norm_bwd(const float* a, const float* b, const float* bias_a, const float* bias_b,
+                                const float* grad_out, int64_t n_rows, int32_t n_nets,
                                 int32_t fa, int32_t fb, float eps, float* grad_a, float* grad_b, void* stream);
 
 /* -- the path's one collective: episode statistics over NCCL --------------------- */

@@ -302,11 +302,20 @@ __global__ void __launch_bounds__(256) relu_l2norm_bwd_kernel(const float* __res
 // for all stacked nets in one pass.  a float32 [N][D][fa], b float32 [N][D][fb] are the two shared input-layer products (bias
 // included), out float32 [D][N][fa + fb] is the layout the stacked dense layers consume.  One warp per (env row, net);
 // fa, fb multiples of 4, fa + fb <= 256 (tanh values stay in registers between the norm and the store).
-__device__ __forceinline__ float4 ld_cat4(const float* ar, const float* br, int fa, int k) {
-  return k < fa ? *reinterpret_cast<const float4*>(ar + k) : *reinterpret_cast<const float4*>(br + (k - fa));
+// element k..k+3 of cat(a_row + bias_a, b_row + bias_b); the bias rows may be null (bias already inside a / b)
+__device__ __forceinline__ float4 ld_cat4(const float* ar, const float* br, const float* ba, const float* bb, int fa, int k) {
+  const bool first = k < fa;
+  float4 v = *reinterpret_cast<const float4*>(first ? ar + k : br + (k - fa));
+  const float* bp = first ? ba : bb;
+  if (bp) {
+    const float4 c = __ldg(reinterpret_cast<const float4*>(bp + (first ? k : k - fa)));
+    v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w;
+  }
+  return v;
 }
 
-__global__ void __launch_bounds__(256) embed_tanh_l2norm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b, long long N, int D, int fa, int fb,
+__global__ void __launch_bounds__(256) embed_tanh_l2norm_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ bias_a,
+                                                                    const float* __restrict__ bias_b, long long N, int D, int fa, int fb,
                                                                     float eps, float* __restrict__ out) {
   const int lane = threadIdx.x & 31, F = fa + fb;
   const long long rows = N * D;
@@ -314,14 +323,17 @@ __global__ void __launch_bounds__(256) embed_tanh_l2norm_fwd_kernel(const float*
   for (long long r = w0; r < rows; r += nw) {
     const float* ar = a + (size_t)r * fa;
     const float* br = b + (size_t)r * fb;
-    float* orow = out + ((size_t)(r % D) * N + (size_t)(r / D)) * F;
+    const int net = (int)(r % D);
+    const float* ba = bias_a ? bias_a + (size_t)net * fa : nullptr;
+    const float* bb = bias_b ? bias_b + (size_t)net * fb : nullptr;
+    float* orow = out + ((size_t)net * N + (size_t)(r / D)) * F;
     float4 y[2];
     float ss = 0.f;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       const int k = lane * 4 + j * 128;
       if (k < F) {
-        const float4 v = ld_cat4(ar, br, fa, k);
+        const float4 v = ld_cat4(ar, br, ba, bb, fa, k);
         y[j] = make_float4(tanhf(v.x), tanhf(v.y), tanhf(v.z), tanhf(v.w));
         ss += y[j].x * y[j].x + y[j].y * y[j].y + y[j].z * y[j].z + y[j].w * y[j].w;
       }
@@ -337,22 +349,25 @@ __global__ void __launch_bounds__(256) embed_tanh_l2norm_fwd_kernel(const float*
 
 // Backward: y = tanh(pre) recomputed, d = max(||y||, eps), g = d loss / d out [D][N][F]:
 //   dy = g / d - y * (g . y) / d^3 (second term only when ||y|| > eps);   dpre = dy * (1 - y^2)  ->  da [N][D][fa], db [N][D][fb]
-__global__ void __launch_bounds__(256) embed_tanh_l2norm_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ g,
-                                                                    long long N, int D, int fa, int fb, float eps, float* __restrict__ da, float* __restrict__ db) {
+__global__ void __launch_bounds__(256) embed_tanh_l2norm_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ bias_a,
+                                                                    const float* __restrict__ bias_b, const float* __restrict__ g, long long N, int D, int fa, int fb, float eps, float* __restrict__ da, float* __restrict__ db) {
   const int lane = threadIdx.x & 31, F = fa + fb;
   const long long rows = N * D;
   const long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
   for (long long r = w0; r < rows; r += nw) {
     const float* ar = a + (size_t)r * fa;
     const float* br = b + (size_t)r * fb;
-    const float* gr = g + ((size_t)(r % D) * N + (size_t)(r / D)) * F;
+    const int net = (int)(r % D);
+    const float* ba = bias_a ? bias_a + (size_t)net * fa : nullptr;
+    const float* bb = bias_b ? bias_b + (size_t)net * fb : nullptr;
+    const float* gr = g + ((size_t)net * N + (size_t)(r / D)) * F;
     float4 y[2], u[2];
     float ss = 0.f, gy = 0.f;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       const int k = lane * 4 + j * 128;
       if (k < F) {
-        const float4 v = ld_cat4(ar, br, fa, k);
+        const float4 v = ld_cat4(ar, br, ba, bb, fa, k);
         u[j] = *reinterpret_cast<const float4*>(gr + k);
         y[j] = make_float4(tanhf(v.x), tanhf(v.y), tanhf(v.z), tanhf(v.w));
         ss += y[j].x * y[j].x + y[j].y * y[j].y + y[j].z * y[j].z + y[j].w * y[j].w;
@@ -376,6 +391,25 @@ __global__ void __launch_bounds__(256) embed_tanh_l2norm_bwd_kernel(const float*
         *reinterpret_cast<float4*>(dst) = t;
       }
     }
+  }
+}
+
+// (x - mean(x)) / std(x) per row, unbiased std (torch.Tensor.std()): the input normalisation of both policy families at batch 1
+// (A2C/models.py:101-103, DQL_model/DQLearning.py:40-42).  x, out float32 [rows][F]; one warp per row, three passes over a row
+// that stays in L1.  F == 1 gives NaN, as torch does.
+__global__ void __launch_bounds__(256) row_standardize_kernel(const float* __restrict__ x, long long rows, int F, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const long long w0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = w0; r < rows; r += nw) {
+    const float* xr = x + (size_t)r * F;
+    float* orow = out + (size_t)r * F;
+    float sum = 0.f;
+    for (int k = lane; k < F; k += 32) sum += xr[k];
+    const float mean = warp_sum(sum) / (float)F;
+    float ss = 0.f;
+    for (int k = lane; k < F; k += 32) { const float d = xr[k] - mean; ss += d * d; }
+    const float sd = sqrtf(warp_sum(ss) / (float)(F - 1));
+    for (int k = lane; k < F; k += 32) orow[k] = (xr[k] - mean) / sd;
   }
 }
 

@@ -642,28 +642,38 @@ extern "C" int swarm_relu_l2norm_bwd(const float* x, const float* grad_out, int6
   return SWARM_OK;
 }
 
-extern "C" int swarm_embed_tanh_l2norm_fwd(const float* a, const float* b, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb, float eps, float* out,
-                                           void* stream) {
-  if (!a || !b || !out || n_rows < 1 || n_nets < 1 || fa < 4 || fb < 4 || (fa & 3) || (fb & 3) || fa + fb > 256 ||
-      (((uintptr_t)a | (uintptr_t)b | (uintptr_t)out) & 15))
-    return SWARM_ERR_INVALID_ARG;
+extern "C" int swarm_row_standardize(const float* x, int64_t rows, int32_t features, float* out, void* stream) {
+  if (!x || !out || rows < 1 || features < 1) return SWARM_ERR_INVALID_ARG;
   int blocks = 0;
-  int rc = row_kernel_blocks(n_rows * n_nets, &blocks);
+  int rc = row_kernel_blocks(rows, &blocks);
   if (rc) return rc;
-  embed_tanh_l2norm_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, b, n_rows, n_nets, fa, fb, eps, out);
+  row_standardize_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, rows, features, out);
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;
 }
 
-extern "C" int swarm_embed_tanh_l2norm_bwd(const float* a, const float* b, const float* grad_out, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb,
-                                           float eps, float* grad_a, float* grad_b, void* stream) {
-  if (!a || !b || !grad_out || !grad_a || !grad_b || n_rows < 1 || n_nets < 1 || fa < 4 || fb < 4 || (fa & 3) || (fb & 3) || fa + fb > 256 ||
-      (((uintptr_t)a | (uintptr_t)b | (uintptr_t)grad_out | (uintptr_t)grad_a | (uintptr_t)grad_b) & 15))
+extern "C" int swarm_embed_tanh_l2norm_fwd(const float* a, const float* b, const float* bias_a, const float* bias_b, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb, float eps, float* out,
+                                           void* stream) {
+  if (!a || !b || !out || n_rows < 1 || n_nets < 1 || fa < 4 || fb < 4 || (fa & 3) || (fb & 3) || fa + fb > 256 ||
+      (((uintptr_t)a | (uintptr_t)b | (uintptr_t)out | (uintptr_t)bias_a | (uintptr_t)bias_b) & 15))
     return SWARM_ERR_INVALID_ARG;
   int blocks = 0;
   int rc = row_kernel_blocks(n_rows * n_nets, &blocks);
   if (rc) return rc;
-  embed_tanh_l2norm_bwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, b, grad_out, n_rows, n_nets, fa, fb, eps, grad_a, grad_b);
+  embed_tanh_l2norm_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, b, bias_a, bias_b, n_rows, n_nets, fa, fb, eps, out);
+  CUDA_TRY(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_embed_tanh_l2norm_bwd(const float* a, const float* b, const float* bias_a, const float* bias_b, const float* grad_out, int64_t n_rows, int32_t n_nets, int32_t fa, int32_t fb,
+                                           float eps, float* grad_a, float* grad_b, void* stream) {
+  if (!a || !b || !grad_out || !grad_a || !grad_b || n_rows < 1 || n_nets < 1 || fa < 4 || fb < 4 || (fa & 3) || (fb & 3) || fa + fb > 256 ||
+      (((uintptr_t)a | (uintptr_t)b | (uintptr_t)grad_out | (uintptr_t)grad_a | (uintptr_t)grad_b | (uintptr_t)bias_a | (uintptr_t)bias_b) & 15))
+    return SWARM_ERR_INVALID_ARG;
+  int blocks = 0;
+  int rc = row_kernel_blocks(n_rows * n_nets, &blocks);
+  if (rc) return rc;
+  embed_tanh_l2norm_bwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, b, bias_a, bias_b, grad_out, n_rows, n_nets, fa, fb, eps, grad_a, grad_b);
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;
 }

@@ -111,8 +111,9 @@ def lib():
         "swarm_nstep_returns": (C.c_int, [vp, vp, vp, i32, i64, i32, C.c_float, vp, vp, vp]),
         "swarm_gru_gates_fwd": (C.c_int, [vp, vp, i64, i32, i32, vp, vp]),
         "swarm_bias_act": (C.c_int, [vp, vp, i32, i64, i32, i32, vp]),
-        "swarm_embed_tanh_l2norm_fwd": (C.c_int, [vp, vp, i64, i32, i32, i32, C.c_float, vp, vp]),
-        "swarm_embed_tanh_l2norm_bwd": (C.c_int, [vp, vp, vp, i64, i32, i32, i32, C.c_float, vp, vp, vp]),
+        "swarm_embed_tanh_l2norm_fwd": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, i32, C.c_float, vp, vp]),
+        "swarm_embed_tanh_l2norm_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, i32, i32, i32, C.c_float, vp, vp, vp]),
+        "swarm_row_standardize": (C.c_int, [vp, i64, i32, vp, vp]),
         "swarm_relu_l2norm_fwd": (C.c_int, [vp, i64, i32, C.c_float, vp, vp]),
         "swarm_relu_l2norm_bwd": (C.c_int, [vp, vp, i64, i32, C.c_float, vp, vp]),
         "swarm_gru_gates_bwd": (C.c_int, [vp, vp, vp, i64, i32, i32, vp, vp, vp]),
@@ -130,7 +131,7 @@ EXPORTED = ("swarm_abi_version swarm_strerror swarm_last_cuda_error swarm_device
             "swarm_get_config swarm_obs_elems swarm_obs_bytes swarm_state_ptr swarm_reset swarm_set_state swarm_get_state "
             "swarm_step swarm_rollout swarm_step_host swarm_stage_move swarm_stage_scatter swarm_stage_reward "
             "swarm_stage_obs swarm_greedy_actions swarm_device_error swarm_launch_count swarm_sample_actions "
-            "swarm_nstep_returns swarm_gru_gates_fwd swarm_gru_gates_bwd swarm_bias_act swarm_embed_tanh_l2norm_fwd swarm_embed_tanh_l2norm_bwd swarm_relu_l2norm_fwd swarm_relu_l2norm_bwd swarm_comm_unique_id swarm_comm_init swarm_comm_destroy swarm_stats_allreduce swarm_stats_mailbox_handle "
+            "swarm_nstep_returns swarm_gru_gates_fwd swarm_gru_gates_bwd swarm_bias_act swarm_embed_tanh_l2norm_fwd swarm_embed_tanh_l2norm_bwd swarm_row_standardize swarm_relu_l2norm_fwd swarm_relu_l2norm_bwd swarm_comm_unique_id swarm_comm_init swarm_comm_destroy swarm_stats_allreduce swarm_stats_mailbox_handle "
             "swarm_stats_peers_open swarm_stats_peers_close swarm_stats_global swarm_stats_push").split()
 
 

@@ -36,33 +36,48 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 class _EmbedTanhL2Norm(torch.autograd.Function):
-    """F.normalize(cat(tanh(a), tanh(b)), dim=-1) for the stacked nets (DQLearning.py:43-46) in one pass each way:
-    a [N, D, fa], b [N, D, fb] float32 CUDA (the shared input-layer products) -> [D, N, fa + fb]
+    """F.normalize(cat(tanh(a + bias_a), tanh(b + bias_b)), dim=-1) for the stacked nets (DQLearning.py:43-46) in one pass each
+    way: a [N, D, fa], b [N, D, fb] float32 CUDA (the shared input-layer products WITHOUT bias — a broadcast bias inside addmm
+    costs a full-size fill and a read of it), bias_a [D, fa], bias_b [D, fb] -> [D, N, fa + fb]
     (swarm_embed_tanh_l2norm_fwd / _bwd)."""
 
     @staticmethod
-    def forward(ctx, a, b):
+    def forward(ctx, a, b, bias_a, bias_b):
         from . import _lib
-        a, b = a.contiguous(), b.contiguous()
+        a, b, bias_a, bias_b = a.contiguous(), b.contiguous(), bias_a.detach().contiguous(), bias_b.detach().contiguous()
         N, D, fa = a.shape
         fb = b.shape[2]
         out = torch.empty((D, N, fa + fb), dtype=torch.float32, device=a.device)
-        _lib.check(_lib.lib().swarm_embed_tanh_l2norm_fwd(a.data_ptr(), b.data_ptr(), N, D, fa, fb, 1e-12, out.data_ptr(),
-                                                          torch._C._cuda_getCurrentRawStream(a.device.index)))
-        ctx.save_for_backward(a, b)
+        _lib.check(_lib.lib().swarm_embed_tanh_l2norm_fwd(a.data_ptr(), b.data_ptr(), bias_a.data_ptr(), bias_b.data_ptr(), N, D, fa, fb,
+                                                          1e-12, out.data_ptr(), torch._C._cuda_getCurrentRawStream(a.device.index)))
+        ctx.save_for_backward(a, b, bias_a, bias_b)
         return out
 
     @staticmethod
     def backward(ctx, g):
         from . import _lib
-        a, b = ctx.saved_tensors
+        a, b, bias_a, bias_b = ctx.saved_tensors
         N, D, fa = a.shape
         fb = b.shape[2]
         g = g.contiguous()
         da, db = torch.empty_like(a), torch.empty_like(b)
-        _lib.check(_lib.lib().swarm_embed_tanh_l2norm_bwd(a.data_ptr(), b.data_ptr(), g.data_ptr(), N, D, fa, fb, 1e-12, da.data_ptr(),
-                                                          db.data_ptr(), torch._C._cuda_getCurrentRawStream(a.device.index)))
-        return da, db
+        _lib.check(_lib.lib().swarm_embed_tanh_l2norm_bwd(a.data_ptr(), b.data_ptr(), bias_a.data_ptr(), bias_b.data_ptr(), g.data_ptr(),
+                                                          N, D, fa, fb, 1e-12, da.data_ptr(), db.data_ptr(),
+                                                          torch._C._cuda_getCurrentRawStream(a.device.index)))
+        return da, db, da.sum(0), db.sum(0)
+
+
+def row_standardize(x):
+    """(x - mean) / std per row, unbiased std — `(state - state.mean()) / state.std()` at batch 1 (DQLearning.py:40-42); one
+    kernel (swarm_row_standardize) for float32 CUDA rows, the torch expression otherwise.  No gradient (inputs are data)."""
+    if x.is_cuda and x.dtype == torch.float32 and not x.requires_grad:
+        from . import _lib
+        x = x.contiguous()
+        out = torch.empty_like(x)
+        _lib.check(_lib.lib().swarm_row_standardize(x.data_ptr(), x.shape[0], x.shape[1], out.data_ptr(),
+                                                    torch._C._cuda_getCurrentRawStream(x.device.index)))
+        return out
+    return (x - x.mean(dim=1, keepdim=True)) / x.std(dim=1, keepdim=True)
 
 
 # (name in AgentModel, in_features, out_features); S = state_size, D = n_drones, A = action_size   (DQLearning.py:30-34)
@@ -104,10 +119,12 @@ class BatchedQNet(nn.Module):
         from .a2c import _StackedLinear
         return _StackedLinear.apply(x, getattr(self, f"{name}__weight"), getattr(self, f"{name}__bias"), act, bool(self.fused))
 
-    def _lin_shared(self, x, name):
+    def _lin_shared(self, x, name, bias=True):
         """-> [N, D, out]: the layer of every net applied to the same rows."""
         w, b = getattr(self, f"{name}__weight"), getattr(self, f"{name}__bias")
         D, fo, fi = w.shape
+        if not bias:
+            return torch.mm(x, w.reshape(D * fo, fi).t()).view(x.shape[0], D, fo)
         return torch.addmm(b.reshape(1, D * fo), x, w.reshape(D * fo, fi).t()).view(x.shape[0], D, fo)
 
     def forward(self, state, drone_pos):
@@ -117,15 +134,15 @@ class BatchedQNet(nn.Module):
         dt = self.state_input__weight.dtype
         N = state.shape[0]
         s = state.reshape(N, self.state_size).to(dt)
-        mu = s.mean(dim=1, keepdim=True)                                    # :40-42 at batch 1
-        std = s.std(dim=1, keepdim=True)                                    # unbiased, as torch.Tensor.std()
-        s = (s - mu) / std
+        fused = self.fused and s.is_cuda and dt == torch.float32
+        s = row_standardize(s) if fused else (s - s.mean(dim=1, keepdim=True)) / s.std(dim=1, keepdim=True)   # :40-42 at batch 1
         p = drone_pos.reshape(N, 2 * D).to(dt)
         # the two input layers see the same rows in every net: ONE [N, in] x [in, D*64] product each instead of D
-        ea, eb = self._lin_shared(s, "state_input"), self._lin_shared(p, "drone_input")
-        if self.fused and ea.is_cuda and ea.dtype == torch.float32:
-            out = _EmbedTanhL2Norm.apply(ea, eb)                            # tanh + cat + F.normalize + [N, D] -> [D, N] in one pass
+        if fused:                                                           # bias + tanh + cat + F.normalize + [N, D] -> [D, N] in one pass
+            out = _EmbedTanhL2Norm.apply(self._lin_shared(s, "state_input", False), self._lin_shared(p, "drone_input", False),
+                                         self.state_input__bias, self.drone_input__bias)
         else:
+            ea, eb = self._lin_shared(s, "state_input"), self._lin_shared(p, "drone_input")
             out = F.normalize(torch.cat([ea, eb], dim=-1).transpose(0, 1).tanh(), dim=-1)   # :43-46 (L2 over features, eps 1e-12)
         out = self._lin(out, "dense1", 2)                                   # :47-48 torch.tanh(dense(.))
         out = self._lin(out, "dense2", 2)

@@ -114,13 +114,15 @@ def test_fused_embedding_matches_torch(N, D, fa, fb):
     b = torch.randn((N, D, fb), device="cuda", generator=gen) * 2
     a[0, 0], b[0, 0] = 0.0, 0.0
     gw = torch.randn((D, N, fa + fb), device="cuda", generator=gen)
-    ref = lambda x, y: F.normalize(torch.cat([x, y], dim=-1).transpose(0, 1).tanh(), dim=-1)   # noqa: E731
+    ba, bb_ = torch.randn((D, fa), device="cuda", generator=gen), torch.randn((D, fb), device="cuda", generator=gen)
+    ba[0], bb_[0] = 0.0, 0.0                                                 # keeps row (0, 0) at zero
+    ref = lambda x, y, p, q: F.normalize(torch.cat([x + p, y + q], dim=-1).transpose(0, 1).tanh(), dim=-1)   # noqa: E731
     res = []
     for fn, dt in ((_EmbedTanhL2Norm.apply, torch.float32), (ref, torch.float32), (ref, torch.float64)):
-        aa, bb = (t.to(dt).clone().requires_grad_(True) for t in (a, b))
-        o = fn(aa, bb)
+        aa, bb, pp, qq = (t.to(dt).clone().requires_grad_(True) for t in (a, b, ba, bb_))
+        o = fn(aa, bb, pp, qq)
         (o * gw.to(dt)).sum().backward()
-        res.append((o.detach().double(), aa.grad.double(), bb.grad.double()))
+        res.append((o.detach().double(), aa.grad.double(), bb.grad.double(), pp.grad.double(), qq.grad.double()))
     for got, t32, t64 in zip(*res):
         scale = max(1.0, float(t64.abs().max()))
         err_f, err_t = float((got - t64).abs().max()) / scale, float((t32 - t64).abs().max()) / scale
@@ -150,3 +152,19 @@ def test_fused_qnet_equals_unfused():
         outs.append([q.detach(), loss.detach()] + [p.grad.clone() for p in net.parameters()])
     for a, r in zip(*outs):
         torch.testing.assert_close(a, r, rtol=2e-4, atol=2e-5 * max(1.0, float(r.abs().max())))
+
+
+@pytest.mark.parametrize("rows,F", [(1000, 100), (7, 25), (33, 4096), (5, 2)])
+def test_row_standardize_matches_torch(rows, F):
+    from swarm_b200.dql import row_standardize
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    x = torch.randint(0, 6, (rows, F), device="cuda", generator=gen).float()
+    x[0] = torch.arange(F, device="cuda").float()
+    got = row_standardize(x).double()
+    x64 = x.double()
+    want64 = (x64 - x64.mean(1, keepdim=True)) / x64.std(1, keepdim=True)
+    want32 = ((x - x.mean(1, keepdim=True)) / x.std(1, keepdim=True)).double()
+    ok = torch.isfinite(want64)
+    assert torch.equal(torch.isfinite(got), ok)                              # constant rows: 0 / 0 like torch
+    err_f, err_t = float((got - want64)[ok].abs().max()), float((want32 - want64)[ok].abs().max())
+    assert err_f <= 2.0 * err_t + 1e-6, (err_f, err_t)
