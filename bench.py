@@ -106,12 +106,21 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def host_cores():
+    """Cores this process may run on.  torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arms ignore it and use every
+    core of the box (the N >= 2 reference arms ran on one thread)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def cpu_port_throughput(kw, budget_s=12.0, scan_mode=0, threads=0, steps=None):
     """Times the oracle port of the reference algorithm (literal R*C scan per drone, A2C/noVis_sim.py:75-90) on the host
     cores: a bounded sample of the same workload shape.  Returns (agent_steps_per_s, cores, sample description)."""
     import numpy as np
-    from oracle.oracle import OracleBatch, lib
-    cores = threads or (lib().oracle_max_threads())
+    from oracle.oracle import OracleBatch
+    cores = threads or host_cores()
     om = 0 if kw["obs_mode"] == "full" else 1
     okw = dict(row_count=kw["row_count"], col_count=kw["col_count"], n_drones=kw["n_drones"], step_size=kw["step_size"],
                obs_mode=om, window=kw.get("window", 5), auto_reset=True, seed=2026, scan_mode=scan_mode, nthreads=cores)
@@ -132,40 +141,81 @@ def cpu_port_throughput(kw, budget_s=12.0, scan_mode=0, threads=0, steps=None):
     return v, cores, sample, wall / T
 
 
+def python_reference_throughput(kw, steps, warmup, budget_s):
+    """The UNMODIFIED reference DroneEnv (baseline/_ref/A2C/noVis_sim.py) on every host core: P worker processes, no per-step
+    IPC (baseline/ref_runner.py; SURVEY §8(d) primary CPU baseline).  Runs in a child interpreter so that the workers are
+    forked from a process that never touched CUDA.  Returns the runner's dict, or None when baseline/_ref is not installed."""
+    runner = os.path.join(REPO, "baseline", "ref_runner.py")
+    cmd = [sys.executable, runner, "--steps", str(steps), "--warmup", str(warmup), "--budget-s", str(budget_s),
+           "--procs", str(host_cores()), "--row_count", str(kw["row_count"]), "--col_count", str(kw["col_count"]),
+           "--n_drones", str(kw["n_drones"]), "--step_size", str(kw["step_size"])]
+    env = dict(os.environ)
+    env.pop("OMP_NUM_THREADS", None)
+    try:
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=budget_s * 4 + 120, env=env)
+        d = json.loads(p.stdout.strip().splitlines()[-1])
+    except Exception as exc:
+        print(f"[bench] python reference runner failed: {exc!r}", file=sys.stderr)
+        return None
+    return None if "unavailable" in d else d
+
+
+def reference_sample_text(r, workload):
+    return (f"each step = {r['inner']} env-steps of {r['procs'] * r['envs_per_proc']} envs (bounded sample of {workload}: the shape is the "
+            f"workload's, the env count is not — CPU throughput does not depend on it), UNMODIFIED A2C/noVis_sim.py DroneEnv from "
+            f"baseline/_ref, {r['procs']} worker processes, reset on done, random actions, {r['wall_s']:.1f} s")
+
+
 def run_reference(args, kw, n_envs, rank, world):
-    """--impl reference: the reference's own CPU implementation of the path (oracle port, all host threads), rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path on every host core, rank 0 only.  Primary: the
+    unmodified Python DroneEnv installed under baseline/_ref (kind "reference"); the oracle's C/OpenMP port of the same
+    algorithm (kind "port", far faster than the reference itself) is reported beside it as `cpu_port`, and is the fallback
+    when baseline/_ref is absent."""
     if rank != 0:
         return
     steps, warm = max(args.steps, 1), max(args.warmup, 0)
-    import numpy as np
-    from oracle.oracle import OracleBatch, lib
-    cores = lib().oracle_max_threads()
-    om = 0 if kw["obs_mode"] == "full" else 1
-    n_cpu = 8 * cores
-    o = OracleBatch(n_cpu, row_count=kw["row_count"], col_count=kw["col_count"], n_drones=kw["n_drones"],
-                    step_size=kw["step_size"], obs_mode=om, window=kw.get("window", 5), auto_reset=True, seed=2026,
-                    scan_mode=0, nthreads=cores)
-    acts = np.random.RandomState(1234).randint(0, 4, (16, n_cpu, kw["n_drones"])).astype(np.uint8)
-    t0 = time.perf_counter(); o.step(acts[0]); dt = max(time.perf_counter() - t0, 1e-6)
-    inner = max(1, min(5000, int(120.0 / (steps + warm) / dt)))      # whole run stays within ~2 minutes
-    for w in range(warm):
-        for k in range(inner):
-            o.step(acts[k % 16])
-    t0 = time.perf_counter()
-    for s in range(steps):
-        for k in range(inner):
-            o.step(acts[k % 16])
-    wall = time.perf_counter() - t0
-    v = n_cpu * kw["n_drones"] * inner * steps / wall
-    sample = (f"each step = {inner} env-steps of {n_cpu} envs (bounded sample of {args.workload}), literal R*C-scan C port of "
-              f"A2C/noVis_sim.py (OpenMP, {cores} threads)")
-    print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
-        "ms_per_step": wall / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": {"workload": args.workload, **{k: v2 for k, v2 in kw.items()}, "envs_per_step": n_cpu},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    cores = host_cores()
+    cfg = {"workload": args.workload, **{k: v2 for k, v2 in kw.items()}}
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic"}
+    r = python_reference_throughput(kw, steps, warm, budget_s=min(60.0, 10.0 + 2.5 * (steps + warm)))
+    if r is not None:
+        port_v, _, port_sample, _ = cpu_port_throughput(kw, budget_s=8.0, scan_mode=0, threads=cores)
+        v = r["value"]
+        cfg.update(total_envs=r["procs"] * r["envs_per_proc"], env_steps_per_step=r["inner"],
+                   note="bounded sample: P = host cores envs of the workload's shape, not the workload's env count")
+        line.update(value=v, ms_per_step=r["wall_s"] / steps * 1e3, config=cfg,
+                    cpu_baseline={"value": v, "unit": UNIT, "cores": r["procs"], "kind": "reference",
+                                  "sample": reference_sample_text(r, args.workload)},
+                    cpu_port={"value": port_v, "unit": UNIT, "cores": cores, "kind": "port", "sample": port_sample})
+    else:
+        import numpy as np
+        from oracle.oracle import OracleBatch
+        om = 0 if kw["obs_mode"] == "full" else 1
+        n_cpu = 8 * cores
+        o = OracleBatch(n_cpu, row_count=kw["row_count"], col_count=kw["col_count"], n_drones=kw["n_drones"],
+                        step_size=kw["step_size"], obs_mode=om, window=kw.get("window", 5), auto_reset=True, seed=2026,
+                        scan_mode=0, nthreads=cores)
+        acts = np.random.RandomState(1234).randint(0, 4, (16, n_cpu, kw["n_drones"])).astype(np.uint8)
+        t0 = time.perf_counter(); o.step(acts[0]); dt = max(time.perf_counter() - t0, 1e-6)
+        inner = max(1, min(5000, int(120.0 / (steps + warm) / dt)))      # whole run stays within ~2 minutes
+        for w in range(warm):
+            for k in range(inner):
+                o.step(acts[k % 16])
+        t0 = time.perf_counter()
+        for s in range(steps):
+            for k in range(inner):
+                o.step(acts[k % 16])
+        wall = time.perf_counter() - t0
+        v = n_cpu * kw["n_drones"] * inner * steps / wall
+        cfg.update(total_envs=n_cpu, env_steps_per_step=inner,
+                   note="baseline/_ref not installed: the oracle's C port of the reference algorithm stands in")
+        sample = (f"each step = {inner} env-steps of {n_cpu} envs (bounded sample of {args.workload}), literal R*C-scan C port of "
+                  f"A2C/noVis_sim.py (OpenMP, {cores} threads)")
+        line.update(value=v, ms_per_step=wall / steps * 1e3, config=cfg,
+                    cpu_baseline={"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample})
+    line["e2e"] = {"value": line["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    print(json.dumps(line))
 
 
 _REAL_STDOUT = None
@@ -187,6 +237,39 @@ def emit(line):
         sys.stdout.write(data.decode()); sys.stdout.flush()
     else:
         os.write(_REAL_STDOUT, data)
+
+
+def teardown(dev, world, envs, comm=None, graphs=()):
+    """Orderly exit (no os._exit: the interpreter's exit handlers must run so that the driver's hook sees which .so files
+    this process mapped).  Order matters: captured graphs first (they reference the env buffers and, in --stats-mode nccl,
+    NCCL work), then a barrier so that no peer is still pushing statistics into this rank's mailbox, then the peer mappings,
+    the library communicator, the env handles, and the process group last."""
+    import torch
+    import torch.distributed as dist
+    sys.stdout.flush()
+    for g in graphs:
+        if g is not None:
+            g.reset()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+    for e in envs:
+        try:
+            e.disable_peer_stats()
+        except Exception:
+            pass
+    if world > 1:
+        dist.barrier()
+    if comm is not None:
+        comm.close()
+    for e in envs:
+        e.close()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sys.stdout.flush(); sys.stderr.flush()
 
 
 def run_a2c(args, rank, world, local):
@@ -297,13 +380,7 @@ def run_a2c(args, rank, world, local):
             "cpu_baseline": {"value": 47.2, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified A2C/train.py::train(), 250 env-steps, 10x10, 8 drones, MLP, measured in the build container (cannot travel to the GPU box)"},
         }
         emit(line)
-    sys.stdout.flush()
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-    env.close()
-    sys.stdout.flush(); sys.stderr.flush()
-    os._exit(0)
+    teardown(dev, world, [env])
 
 
 def run_dql(args, rank, world, local):
@@ -401,13 +478,247 @@ def run_dql(args, rank, world, local):
             "cpu_baseline": {"value": 15.9, "unit": UNIT, "cores": 8, "kind": "reference", "sample": "unmodified DQLearning.py Agent + env loop, 60 env-steps with replay(32), 10x10, 8 drones, measured in the build container by tools/dql_ref_cpu.py (cannot travel to the GPU box)"},
         }
         emit(line)
-    sys.stdout.flush()
+    teardown(dev, world, [env])
+
+
+class StepLoop:
+    """`sets` independent env batches of n_envs envs each (rotated so that the working set exceeds L2), 32 pre-generated action
+    tensors, and the timed loop: K consecutive steps as CUDA-graph replays — floor(K / 32) replays of a 32-step graph plus ONE
+    replay of a (K mod 32)-step graph — so the timed region holds nothing but step kernels whatever --steps is."""
+
+    N_ACT = 32
+
+    def __init__(self, torch, dev, n_envs, kw, sets, obs_dt, id_base, rank, use_graph=True, id_stride=None):
+        from swarm_b200 import BatchedDroneEnv
+        self.torch, self.dev, self.n_envs, self.sets, self.kw = torch, dev, n_envs, sets, kw
+        D = kw["n_drones"]
+        self.envs = [BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=id_base + s * (id_stride or n_envs), obs_dtype=obs_dt, **kw)
+                     for s in range(sets)]
+        self.obs = [torch.empty(e.obs_shape, dtype=obs_dt, device=dev) for e in self.envs]
+        gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+        # 32 pre-generated action tensors: 16 i.i.d. uniform draws followed by their opposites ((a+2) mod 4), so a cycle has no
+        # net drift and the drones keep wandering instead of piling up against a wall over thousands of steps.
+        half = torch.randint(0, 4, (16, n_envs, D), dtype=torch.uint8, device=dev, generator=gen)
+        self.acts = torch.cat([half, (half + 2) % 4]).contiguous()
+        self.use_graph = use_graph and self.N_ACT % sets == 0
+        self.graphs = {}            # n steps -> CUDAGraph of steps 0 .. n-1
+        self.hook = None            # optional per-step callable(i, env) enqueued after the step (NCCL statistics form)
+
+    def one_step(self, i, ev=None):
+        s = i % self.sets
+        if ev is not None:
+            ev[0].record(self.torch.cuda.current_stream(self.dev))
+        self.envs[s].step(self.acts[i % self.N_ACT], out=self.obs[s])
+        if ev is not None:
+            ev[1].record(self.torch.cuda.current_stream(self.dev))
+        if self.hook is not None:
+            self.hook(i, self.envs[s])
+
+    def graph_for(self, n, tail=None):
+        """CUDA graph of steps 0 .. n-1 (captured once, replayed once as warm-up).  None when capture is off / impossible."""
+        torch = self.torch
+        if not self.use_graph or n <= 0:
+            return None
+        if n not in self.graphs:
+            try:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    for j in range(n):
+                        self.one_step(j)
+                    if tail is not None:
+                        tail()
+                g.replay()
+                torch.cuda.synchronize(self.dev)
+                self.graphs[n] = g
+            except Exception as exc:    # capture unsupported (e.g. a collective that refuses capture): eager launches
+                print(f"[bench] CUDA graph capture of {n} steps failed ({exc!r}); falling back to eager launches", file=sys.stderr)
+                self.use_graph = False
+                torch.cuda.synchronize(self.dev)
+                return None
+        return self.graphs[n]
+
+    def plan(self, count, tail=None):
+        """(full replays, remainder) of `count` steps and the graphs they need; eager when graphs are off."""
+        full, rem = divmod(count, self.N_ACT)
+        gf = self.graph_for(self.N_ACT, tail) if full else None
+        gr = self.graph_for(rem, tail) if rem else None
+        if (full and gf is None) or (rem and gr is None):
+            return None
+        return full, gf, gr
+
+    def run(self, count, plan=None, ev=None):
+        """`count` consecutive steps starting at step index 0 (mod 32)."""
+        if plan is not None and ev is None:
+            full, gf, gr = plan
+            for _ in range(full):
+                gf.replay()
+            if gr is not None:
+                gr.replay()
+            return
+        for k in range(count):
+            self.one_step(k, None if ev is None else ev[k])
+
+    def describe(self, count, plan):
+        if plan is None:
+            return "eager (one swarm_step call per step from Python)"
+        full, rem = divmod(count, self.N_ACT)
+        parts = ([f"{full} x {self.N_ACT}-step graph"] if full else []) + ([f"1 x {rem}-step graph"] if rem else [])
+        return "CUDA graph replay: " + " + ".join(parts)
+
+    def close(self):
+        for g in self.graphs.values():
+            g.reset()
+        self.graphs = {}
+
+
+def time_steps(torch, dist, dev, world, loop, K, plan, tail_sync=None):
+    """Device time of exactly K steps, bracketed by barrier + synchronize, max over ranks (ms)."""
+    stream = torch.cuda.current_stream(dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record(stream)
+    loop.run(K, plan)
+    if tail_sync is not None:
+        tail_sync()
+    t1.record(stream)
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
-    env.close()
-    sys.stdout.flush(); sys.stderr.flush()
-    os._exit(0)
+    ms = t0.elapsed_time(t1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def measure_e2e(torch, dist, dev, world, env, acts_host, obs_dt, E):
+    """E steps through swarm_step_host: pinned HOST buffers in and out, H2D actions + D2H obs / reward / done / statistics and a
+    stream synchronize inside every call.  Returns (ms total as max over ranks, d2h bytes per step)."""
+    n_envs = env.num_envs
+    obs_h = torch.empty(env.obs_shape, dtype=obs_dt).pin_memory()
+    rew_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
+    done_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
+    stats_h = torch.zeros(8, dtype=torch.int64).pin_memory()
+    n_act = acts_host.shape[0]
+    for i in range(3):
+        env.step_host(acts_host[i % n_act], obs_h, rew_h, done_h, stats_h)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    for i in range(E):
+        env.step_host(acts_host[i % n_act], obs_h, rew_h, done_h, stats_h)
+    ms = (time.perf_counter() - w0) * 1e3
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    d2h = int(obs_h.numel() * obs_h.element_size() + n_envs * 4 + n_envs + 64)
+    return ms, d2h
+
+
+def measure_strong(torch, dist, dev, world, rank, kw, total_envs, args, value_1gpu, ms_step_1gpu, weak_loop):
+    """Strong scaling of the workload: `total_envs` envs sharded over the ranks (contiguous env-id ranges, no data-path
+    collective).  Two launch forms, both timed on the device as the max over ranks:
+      single-step: one swarm_step launch per env step, 32 of them per CUDA graph (the policy-in-the-loop form);
+      rollout:     swarm_rollout — T env steps per launch from actions[T, N, D], observations of every step written to
+                   obs[T, N, D, W*W] (grid / positions / meta stay on chip between the T steps).
+    At 1 GPU the single-step form IS the weak-scaling measurement (same envs per GPU), so its numbers are reused."""
+    D = kw["n_drones"]
+    per = total_envs // world
+    bytes_env = algorithmic_bytes_per_env_step(kw)
+    peak, _ = load_peak()
+    out = {"total_envs": per * world, "envs_per_gpu": per, "scaling": "strong", "rollout_T": args.rollout_T}
+    Ks = max(32, args.strong_steps // 32 * 32)
+    if world == 1:
+        loop, own = weak_loop, False
+        sets_s = weak_loop.sets
+        ms = ms_step_1gpu * Ks
+    else:
+        sets_s = 2
+        while sets_s < 16 and sets_s * per * 2437 < 300e6:
+            sets_s *= 2
+        # env ids: batch s of rank g = [s * total + g * per, s * total + (g + 1) * per) — contiguous ranges per rank
+        loop, own = StepLoop(torch, dev, per, kw, sets_s, torch.float32, rank * per, rank, use_graph=not args.no_graph,
+                             id_stride=per * world), True
+        for i in range(4):
+            loop.one_step(i)
+        torch.cuda.synchronize(dev)
+        plan = loop.plan(Ks)
+        if dist.is_initialized():
+            flag = torch.tensor([1 if plan is not None else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 0:
+                plan = None
+        loop.run(Ks, plan)                  # warm
+        ms = time_steps(torch, dist, dev, world, loop, Ks, plan)
+        out["single_step_launch"] = loop.describe(Ks, plan)
+    us = ms / Ks * 1e3
+    out["single_step"] = {"us_per_step": us, "value": float(per) * world * D / (us * 1e-6), "unit": UNIT,
+                          "roofline_frac": bytes_env * per / (us * 1e-6) / 1e9 / peak, "steps": Ks, "env_batches_rotated": sets_s}
+    # rollout form: T steps per launch, one graph of 2 rollouts per env batch
+    T = max(1, args.rollout_T)
+    envs = loop.envs
+    acts_T = loop.acts[:T].contiguous() if T <= loop.N_ACT else loop.acts.repeat((T + 31) // 32, 1, 1)[:T].contiguous()
+    obs_T = torch.empty((T,) + tuple(envs[0].obs_shape), dtype=torch.float32, device=dev)
+    rew_T = torch.empty((T, per), dtype=torch.float32, device=dev)
+    done_T = torch.empty((T, per), dtype=torch.uint8, device=dev)
+
+    def rollouts():
+        for _ in range(2):
+            for e in envs:
+                e.rollout(acts_T, obs_out=obs_T, reward_out=rew_T, done_out=done_T)
+    rollouts()
+    torch.cuda.synchronize(dev)
+    g = None
+    if not args.no_graph:
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                rollouts()
+            g.replay()
+            torch.cuda.synchronize(dev)
+        except Exception as exc:
+            print(f"[bench] rollout graph capture failed ({exc!r}); eager", file=sys.stderr)
+            g = None
+    if world > 1:
+        flag = torch.tensor([1 if g is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            g = None
+    steps_per = 2 * len(envs) * T
+    reps = max(1, Ks // steps_per)
+    stream = torch.cuda.current_stream(dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record(stream)
+    for _ in range(reps):
+        g.replay() if g is not None else rollouts()
+    t1.record(stream)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    msr = t0.elapsed_time(t1)
+    if world > 1:
+        t = torch.tensor([msr], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        msr = float(t.item())
+    usr = msr / (reps * steps_per) * 1e3
+    out["rollout"] = {"us_per_step": usr, "value": float(per) * world * D / (usr * 1e-6), "unit": UNIT,
+                      "roofline_frac": bytes_env * per / (usr * 1e-6) / 1e9 / peak, "steps": reps * steps_per,
+                      "launch": ("CUDA graph of " if g is not None else "eager: ") + f"{2 * len(envs)} swarm_rollout(T={T}) launches, obs of every step written",
+                      "obs_buffer_mb": obs_T.numel() * 4 / 1e6}
+    del obs_T
+    if own:
+        loop.close()
+        for e in envs:
+            e.close()
+    return out
 
 
 def main():
@@ -425,11 +736,14 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
     ap.add_argument("--e2e-steps", type=int, default=20)
-    ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of replaying a CUDA graph of 32 steps")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of replaying CUDA graphs")
     ap.add_argument("--clock-window-s", type=float, default=0.4, help="seconds of identical untimed steps run under the clock sampler right before the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the extra strong-scaling measurement of the default cfg3 line")
+    ap.add_argument("--strong-steps", type=int, default=256)
+    ap.add_argument("--rollout-T", type=int, default=16, help="strong scaling: env steps per swarm_rollout launch")
     ap.add_argument("--stats-mode", default="peer", choices=["peer", "nccl"],
-                    help="N > 1: how the per-step episode statistics cross GPUs — 'peer': pushed by the step kernel's last CTA into "
+                    help="N > 1: how the per-step episode statistics cross GPUs — 'peer': pushed by the step kernel into "
                          "every rank's mailbox over NVLink peer memory (no collective kernel); 'nccl': swarm_stats_allreduce on a side stream")
     ap.add_argument("--stats-every", type=int, default=1, help="N > 1: all-reduce the episode statistics every K steps (0 = never)")
     args = ap.parse_args()
@@ -441,6 +755,7 @@ def main():
         return run_dql(args, rank, world, local)
     n_envs, kw = WORKLOADS[args.workload]
     kw = dict(kw)
+    workload_envs = n_envs
     if args.envs:
         n_envs = args.envs
     if args.scaling == "strong":
@@ -460,18 +775,11 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     D = kw["n_drones"]
-    K, W = args.steps, max(args.warmup, 3)
+    K, W = max(args.steps, 1), max(args.warmup, 3)
     obs_dt = torch.float32 if args.obs_dtype == "float32" else torch.uint8
     s_o = 4 if args.obs_dtype == "float32" else 1
-    envs = [BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=(rank * args.sets + s) * n_envs, obs_dtype=obs_dt, **kw)
-            for s in range(args.sets)]
-    obs = [torch.empty(e.obs_shape, dtype=obs_dt, device=dev) for e in envs]
-    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    # 32 pre-generated action tensors: 16 i.i.d. uniform draws followed by their opposites ((a+2) mod 4), so a cycle has no
-    # net drift and the drones keep wandering instead of piling up against a wall over thousands of steps.
-    half = torch.randint(0, 4, (16, n_envs, D), dtype=torch.uint8, device=dev, generator=gen)
-    acts = torch.cat([half, (half + 2) % 4]).contiguous()
-    n_act = acts.shape[0]
+    loop = StepLoop(torch, dev, n_envs, kw, args.sets, obs_dt, rank * args.sets * n_envs, rank, use_graph=not args.no_graph)
+    envs, n_act = loop.envs, loop.N_ACT
     stream = torch.cuda.current_stream(dev)
     comm = None
     use_nccl = world > 1 and args.stats_mode == "nccl"
@@ -492,67 +800,39 @@ def main():
                     e.disable_peer_stats()
                 except Exception:
                     pass
-    side = None
+    side, tail = None, None
     if use_nccl:
         from swarm_b200 import StatsComm
         comm = StatsComm()
         side = torch.cuda.Stream(dev)       # the all-reduce runs beside the step stream
-    snaps = [torch.zeros(8, dtype=torch.int64, device=dev) for _ in range(n_act)]
+        snaps = [torch.zeros(8, dtype=torch.int64, device=dev) for _ in range(n_act)]
 
-    def one_step(i, ev=None):
-        s = i % args.sets
-        cur = torch.cuda.current_stream(dev)
-        if ev is not None:
-            ev[0].record(cur)
-        envs[s].step(acts[i % n_act], out=obs[s])
-        if ev is not None:
-            ev[1].record(cur)
-        if use_nccl and i % max(args.stats_every, 1) == 0:   # the path's only collective: 64-byte episode statistics
-            snap = snaps[i % n_act]
-            snap.copy_(envs[s].stats, non_blocking=True)
-            side.wait_stream(cur)
-            with torch.cuda.stream(side):
-                comm.allreduce(snap)        # swarm_stats_allreduce: ncclAllReduce(SUM, int64[8]) on the library's communicator
+        def hook(i, env):                   # the path's only collective: 64-byte episode statistics
+            if i % max(args.stats_every, 1) == 0:
+                cur = torch.cuda.current_stream(dev)
+                snap = snaps[i % n_act]
+                snap.copy_(env.stats, non_blocking=True)
+                side.wait_stream(cur)
+                with torch.cuda.stream(side):
+                    comm.allreduce(snap)    # swarm_stats_allreduce: ncclAllReduce(SUM, int64[8]) on the library's communicator
+        loop.hook = hook
 
-    for i in range(W):
-        one_step(i)
-    if side is not None:
-        stream.wait_stream(side)
+        def tail():
+            torch.cuda.current_stream(dev).wait_stream(side)
+
+    for i in range(W):                      # W eager warm-up steps (the graphs get one warm-up replay each on top)
+        loop.one_step(i)
+    if tail is not None:
+        tail()
     torch.cuda.synchronize(dev)
 
-    # CUDA graph of n_act consecutive steps (+ their side-stream all-reduces): the host enqueues one graph per 32 steps
-    # instead of 32 launches, so a microsecond-scale step is not bound by Python call overhead.
-    graph = None
-    if not args.no_graph and n_act % args.sets == 0:
-        try:
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                for j in range(n_act):
-                    one_step(j)
-                if side is not None:
-                    torch.cuda.current_stream(dev).wait_stream(side)
-            graph.replay()
-            torch.cuda.synchronize(dev)
-        except Exception as exc:            # capture unsupported (e.g. a collective that refuses capture): eager launches
-            print(f"[bench] CUDA graph capture failed ({exc!r}); falling back to eager launches", file=sys.stderr)
-            graph = None
-            torch.cuda.synchronize(dev)
-    if world > 1:                           # all ranks must agree (each step carries a collective)
-        flag = torch.tensor([1 if graph is not None else 0], device=dev)
+    plan = loop.plan(K, tail)
+    hold_plan = loop.plan(n_act, tail)
+    if world > 1:                           # all ranks must agree (in NCCL mode each step carries a collective)
+        flag = torch.tensor([1 if (plan is not None and hold_plan is not None) else 0], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()) == 0:
-            graph = None
-
-    def run_steps(first, count, ev=None):
-        """`count` consecutive steps starting at step index `first` (a multiple of n_act): graph replays + eager remainder."""
-        k = 0
-        if graph is not None and ev is None:
-            while count - k >= n_act:
-                graph.replay()
-                k += n_act
-        while k < count:
-            one_step(first + k, None if ev is None else ev[k])
-            k += 1
+            plan = hold_plan = None
 
     # The timed region of a microsecond-scale step lasts milliseconds, shorter than nvidia-smi's sampling period, so the
     # clock sampler runs over a window of identical untimed steps that leads straight into the K timed ones
@@ -561,153 +841,137 @@ def main():
     if rank == 0:
         sampler.start()
     torch.cuda.synchronize(dev)
-    t0 = time.perf_counter(); run_steps(0, n_act); torch.cuda.synchronize(dev)
+    t0 = time.perf_counter(); loop.run(n_act, hold_plan); torch.cuda.synchronize(dev)
     est = max((time.perf_counter() - t0) / n_act, 5e-6)
     if world > 1:                           # every rank must run the same number of steps
         te = torch.tensor([est], dtype=torch.float64, device=dev)
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
         est = float(te.item())
-    hold = int(min(40000, max(0, args.clock_window_s / est))) // n_act * n_act
-    run_steps(0, hold)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_start.record(stream)
-    run_steps(0, K)
-    if side is not None:
-        stream.wait_stream(side)
-    t_end.record(stream)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
+    hold = int(min(40000, max(0, args.clock_window_s / est))) // n_act
+    for _ in range(hold):
+        loop.run(n_act, hold_plan)
+    ms_total = time_steps(torch, dist, dev, world, loop, K, plan, tail)
     clocks = sampler.stop() if rank == 0 else None
-    ms_total = t_start.elapsed_time(t_end)
     launches = K                            # one step kernel per step (graph replays launch the captured kernels)
-    # per-launch durations: a separate eager pass with an event pair around every launch (not part of `value`)
+    # a second, longer graph-replayed region (diagnostic: shows that `value` does not depend on --steps)
+    K_long = 1024
+    ms_long = time_steps(torch, dist, dev, world, loop, K_long, loop.plan(K_long, tail) if plan is not None else None, tail) if K != K_long else ms_total
+    # per-launch durations: a separate EAGER pass with an event pair around every launch (not part of `value`; includes the
+    # launch gaps Python leaves between kernels)
     P = min(K, 64)
     pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(P)]
-    run_steps(0, P, pairs)
-    if side is not None:
-        stream.wait_stream(side)
+    loop.run(P, None, pairs)
+    if tail is not None:
+        tail()
     torch.cuda.synchronize(dev)
     kern_ms = sorted(a.elapsed_time(b) for a, b in pairs)
     pair_avg_ms = sum(kern_ms) / len(kern_ms)
-    if world > 1:
-        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-    # the stream holds nothing but step kernels back to back, so the mean launch-to-launch time over the timed region
-    # bounds the kernel's duration from above (it includes the inter-kernel gaps): the conservative roofline numerator
+    # under graph replay the stream holds nothing but step kernels back to back, so the mean step-to-step time over the timed
+    # region bounds the kernel's duration from above (it includes the inter-kernel gaps): the conservative roofline numerator
     kern_avg_ms = ms_total / K
     total_agent_steps = float(n_envs) * D * K * world
     value = total_agent_steps / (ms_total * 1e-3)
 
-    # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region)
-    e0 = envs[0]
-    a_h = torch.empty((n_act, n_envs, D), dtype=torch.uint8).pin_memory(); a_h.copy_(acts.cpu())
-    obs_h = torch.empty(e0.obs_shape, dtype=obs_dt).pin_memory()
-    rew_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
-    done_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
-    stats_h = torch.zeros(8, dtype=torch.int64).pin_memory()
-    E = max(1, args.e2e_steps)
-    for i in range(3):
-        envs[i % args.sets].step_host(a_h[i % n_act], obs_h, rew_h, done_h, stats_h)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    w0 = time.perf_counter()
-    for i in range(E):
-        envs[i % args.sets].step_host(a_h[i % n_act], obs_h, rew_h, done_h, stats_h)
-    e2e_ms = (time.perf_counter() - w0) * 1e3
-    if world > 1:
-        t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t.item())
-    e2e_value = float(n_envs) * D * E * world / (e2e_ms * 1e-3)
-    h2d = n_envs * D
-    d2h = int(obs_h.numel() * s_o + n_envs * 4 + n_envs + 64)
-    # the same host-buffer call with uint8 observations (values 0 / 1 / U, pad 255): the reference's obs are small integers
-    # (int64 on the host, A2C/noVis_sim.py:168-170) that callers cast to float32 themselves, so a byte per cell loses nothing
-    # and quarters the PCIe traffic that bounds e2e.  Reported beside, not instead of, the float32 number.
-    e8 = BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=rank * args.sets * n_envs, obs_dtype=torch.uint8, **kw)
-    obs8_h = torch.empty(e8.obs_shape, dtype=torch.uint8).pin_memory()
-    for i in range(3):
-        e8.step_host(a_h[i % n_act], obs8_h, rew_h, done_h, stats_h)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    w0 = time.perf_counter()
-    for i in range(E):
-        e8.step_host(a_h[i % n_act], obs8_h, rew_h, done_h, stats_h)
-    e8_ms = (time.perf_counter() - w0) * 1e3
-    if world > 1:
-        t = torch.tensor([e8_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e8_ms = float(t.item())
-    e8_value = float(n_envs) * D * E * world / (e8_ms * 1e-3)
-    e8.close()
+    # ---- strong scaling of the same workload (BASELINE configs[2]: "65536 envs ... sharded over 1/2/4/8"): the workload's env
+    # count divided over the ranks, contiguous env-id ranges, measured next to the weak-scaling value above
+    strong = None
+    if args.workload == "cfg3" and args.scaling == "weak" and not args.no_strong and not args.envs and args.obs_dtype == "float32":
+        strong = measure_strong(torch, dist, dev, world, rank, kw, workload_envs, args, value if world == 1 else None,
+                                ms_total / K if world == 1 else None, loop)
 
-    stats_global = None
-    if world > 1 and not use_nccl:          # what the mailboxes hold after the run: totals of ALL ranks for env batch 0
+    # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region).
+    # Headline format: uint8 observations (values 0 / 1 / U, pad 255) — the reference's obs are small integers (int64 on the
+    # host, A2C/noVis_sim.py:168-170) that its callers cast to float32 themselves (A2C/train.py:21-24), so a byte per cell is
+    # lossless and quarters the PCIe traffic that bounds this number.  The float32 form is measured and reported beside it.
+    E = max(1, args.e2e_steps)
+    a_h = torch.empty((n_act, n_envs, D), dtype=torch.uint8).pin_memory(); a_h.copy_(loop.acts.cpu())
+    e8 = BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=rank * args.sets * n_envs, obs_dtype=torch.uint8, **kw)
+    e8_ms, e8_d2h = measure_e2e(torch, dist, dev, world, e8, a_h, torch.uint8, E)
+    e8.close()
+    ef = envs[0] if args.obs_dtype == "float32" else BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=rank * args.sets * n_envs, **kw)
+    ef_ms, ef_d2h = measure_e2e(torch, dist, dev, world, ef, a_h, torch.float32, E)
+    if ef is not envs[0]:
+        ef.close()
+    h2d = n_envs * D
+    agent_e2e = float(n_envs) * D * E * world
+
+    # ---- the statistics exchange, checked outside every timed region (N > 1): the mailboxes must hold the totals of ALL ranks
+    stats_global, stats_check = None, "n/a (single rank)"
+    if world > 1 and not use_nccl:
         torch.cuda.synchronize(dev)
         dist.barrier()
-        local = envs[0].stats.clone()
-        tot = local.clone()
-        dist.all_reduce(tot)                # checker only (outside every timed region): NCCL sum of the local totals
+        tot = envs[0].stats.clone()
+        dist.all_reduce(tot)                # checker only: NCCL sum of the local totals
         envs[0].push_stats()                # the in-step feed lags by one launch: publish the final totals explicitly
         torch.cuda.synchronize(dev)
         dist.barrier()
-        stats_global = envs[0].global_stats(min_pushes=1).tolist()
-        assert stats_global == tot.tolist(), (stats_global, tot.tolist())
+        try:
+            stats_global = envs[0].global_stats(min_pushes=1).tolist()
+            stats_check = "ok" if stats_global == tot.tolist() else f"MISMATCH: mailboxes {stats_global} != all-reduce {tot.tolist()}"
+        except Exception as exc:
+            stats_check = f"ERROR: {exc!r}"
+        flag = torch.tensor([1 if stats_check == "ok" else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0 and stats_check == "ok":
+            stats_check = "MISMATCH on another rank"
+    elif world > 1:
+        stats_check = "n/a (--stats-mode nccl)"
+    else:
+        st = envs[0].stats.tolist()
+        stats_check = "ok" if st[1] == st[0] * D and st[0] % n_envs == 0 and st[0] > 0 else f"MISMATCH: {st}"
+
     if rank == 0:
         peak, peak_src = load_peak()
         bytes_per_launch = algorithmic_bytes_per_env_step(kw, s_o=s_o) * n_envs
         achieved = bytes_per_launch / (kern_avg_ms * 1e-3) / 1e9
+        e0 = envs[0]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
-            "dtype": "u2 grid codes / f32 positions+obs (integer rewards)", "data": "synthetic",
+            "dtype": "u1 coverage bits + anomaly list / f32 positions+obs (integer rewards)", "data": "synthetic",
             "config": {"workload": args.workload, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw,
                        "obs_dtype": args.obs_dtype, "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
                        "actions": "uint8 uniform{0..3} (16 draws + their opposites, zero net drift), pre-generated on device",
-                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * s_o + n_envs * 1100) / 1e6:.0f} MB > 126 MB L2",
+                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * s_o + n_envs * 700) / 1e6:.0f} MB > 126 MB L2",
                        "parallelism": f"env-sharded x{world}, no data-path collective; per-step episode statistics: " +
                                       ("published by the step kernel into every rank's mailbox over NVLink peer memory (posted stores at kernel start, no collective kernel)"
                                        if not use_nccl else f"swarm_stats_allreduce (NCCL) on a side stream every {max(args.stats_every, 1)} step(s)")},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": load_traffic(args.workload) if args.obs_dtype == "float32" else None, "peak_source": peak_src, "kernel": "swarm::step_warp_kernel (swarm::step_cta_kernel for cfg5a/cfg5b)",
-                         "kernel_ms_avg": kern_avg_ms, "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
-                         "launch": "CUDA graph of 32 steps" if graph is not None else "eager",
+                         "traffic": load_traffic(args.workload) if args.obs_dtype == "float32" else None, "peak_source": peak_src,
+                         "kernel": "swarm::step_warp_kernel (swarm::step_cta_kernel for cfg5a/cfg5b)",
+                         "kernel_ms_avg": kern_avg_ms, "kernel_ms_avg_how": "timed region / steps: the stream holds only step kernels back to back under graph replay",
+                         "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
+                         "kernel_ms_event_pairs_how": "separate EAGER pass, one CUDA-event pair per launch (diagnostic; includes Python launch gaps)",
+                         "launch": loop.describe(K, plan),
+                         "ms_per_step_1024_steps": ms_long / K_long,
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw, s_o=s_o) / D},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": E, "ms_per_step": e2e_ms / E, "api": "swarm_step_host (pinned host buffers, full obs D2H)"},
-            "e2e_uint8_obs": {"value": e8_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                              "d2h_bytes_per_step": int(obs8_h.numel() + n_envs * 4 + n_envs + 64), "steps": E, "ms_per_step": e8_ms / E},
-            "stats_global_env_batch0": stats_global,
-            "gpu_launches": launches, "clocks": dict(clocks, window=f"{hold} untimed steps + the {K} timed steps, continuous load"),
+            "e2e": {"value": agent_e2e / (e8_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": e8_d2h,
+                    "steps": E, "ms_per_step": e8_ms / E, "obs_format": "uint8 (lossless: the obs values are the integers 0 / 1 / U, pad 255)",
+                    "api": "swarm_step_host (pinned host buffers: H2D actions, D2H obs + reward + done + statistics, stream sync per call)",
+                    "d2h_gbs_per_rank": e8_d2h / (e8_ms / E * 1e-3) / 1e9},
+            "e2e_float32_obs": {"value": agent_e2e / (ef_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": ef_d2h,
+                                "steps": E, "ms_per_step": ef_ms / E, "obs_format": "float32 (what the reference's callers cast to)",
+                                "d2h_gbs_per_rank": ef_d2h / (ef_ms / E * 1e-3) / 1e9},
+            "strong_scaling": strong,
+            "stats_check": stats_check, "stats_global_env_batch0": stats_global,
+            "gpu_launches": launches, "clocks": dict(clocks, window=f"{hold * n_act} untimed steps + the {K} timed steps, continuous load"),
         }
         if world == 1 and not args.no_cpu_baseline:
-            v, cores, sample, _ = cpu_port_throughput(kw, budget_s=12.0, scan_mode=0)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
-            v2, _, sample2, _ = cpu_port_throughput(kw, budget_s=4.0, scan_mode=1)
+            r = python_reference_throughput(kw, steps=2, warmup=1, budget_s=15.0)
+            v, cores, sample, _ = cpu_port_throughput(kw, budget_s=8.0, scan_mode=0)
+            port = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+            if r is not None:
+                line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["procs"], "kind": "reference",
+                                        "sample": reference_sample_text(r, args.workload)}
+                line["cpu_baseline_port"] = port
+            else:
+                line["cpu_baseline"] = port
+            v2, _, sample2, _ = cpu_port_throughput(kw, budget_s=3.0, scan_mode=1)
             line["cpu_baseline_windowed"] = {"value": v2, "unit": UNIT, "cores": cores, "kind": "port (ours: bounded-window scan, not the reference's algorithm)", "sample": sample2}
         emit(line)
-    sys.stdout.flush()
-    # teardown: release the captured graph (it holds NCCL work) before the communicator, and leave without running the
-    # interpreter's module teardown, which can dead-lock on a communicator that was used under graph capture
-    graph = None
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-        torch.cuda.synchronize(dev)
-    for e in envs:
-        e.close()
-    if comm is not None:
-        comm.close()
-    sys.stdout.flush(); sys.stderr.flush()
-    os._exit(0)
+    loop.close()
+    teardown(dev, world, envs, comm)
 
 
 if __name__ == "__main__":
