@@ -51,7 +51,8 @@ typedef enum SwarmStatus {
   SWARM_ERR_CUDA = -3,          /* a CUDA runtime call failed (swarm_last_cuda_error) */
   SWARM_ERR_NO_DEVICE = -4,     /* no CUDA device / wrong architecture: there is NO CPU fallback */
   SWARM_ERR_ALLOC = -5,
-  SWARM_ERR_NCCL = -6
+  SWARM_ERR_NCCL = -6,
+  SWARM_ERR_TIMEOUT = -7        /* the peer-statistics mailboxes never became consistent (swarm_stats_global_host) */
 } SwarmStatus;
 
 enum { SWARM_REWARD_A2C = 0, SWARM_REWARD_DQL = 1 };   /* A2C/noVis_sim.py:141-152,172-173 vs DQL_model/noVis_sim.py:138-148 */
@@ -60,7 +61,7 @@ enum { SWARM_DTYPE_F32 = 0, SWARM_DTYPE_U8 = 1 };      /* obs element type */
 enum { SWARM_ACT_U8 = 0, SWARM_ACT_I32 = 1, SWARM_ACT_I64 = 2 };
 
 /* device error word bits (sticky until swarm_device_error(clear=1)) */
-enum { SWARM_DEVERR_BAD_ACTION = 1 };
+enum { SWARM_DEVERR_BAD_ACTION = 1, SWARM_DEVERR_STATS_TIMEOUT = 4 };
 
 /* statistics vector, int64[8], accumulated with atomics */
 enum {
@@ -88,7 +89,10 @@ typedef struct SwarmConfig {
   int32_t device;          /* CUDA device ordinal                                                */
   int32_t reserved0;
   double  collision_dist;  /* cd collision_dist  (0.5)                                           */
-  double  step_size;       /* ss step_size       (0.5; every trainer passes 1.0)                 */
+  double  step_size;       /* ss step_size       (0.5; every trainer passes 1.0).  Must be a dyadic rational
+                            * m * 2^-k small enough that every reachable coordinate is exact in float32
+                            * (the reference accumulates float64, A2C/noVis_sim.py:121-135); 0.1, 0.3 ... are
+                            * SWARM_ERR_CONFIG rather than a silent drift across `dist < collision_dist`.   */
   uint64_t seed;           /* Philox key for device resets                                       */
   int64_t env_id_base;     /* global id of local env 0 (sharding: rank g owns [g*N, (g+1)*N))    */
 } SwarmConfig;
@@ -169,8 +173,13 @@ int swarm_stage_reward(SwarmEnv* env, const int32_t* cover_reward, float* reward
 /* K4 observation emission for the current state. */
 int swarm_stage_obs(SwarmEnv* env, void* obs_out, void* stream);
 
-/* -- scripted action source (swarmsim-2d/drone.py:29-58 restated on the noVis lattice) ------- */
-/* Greedy nearest-unmapped-cell pursuit restricted to the 4 noVis actions; writes uint8[N][D]. */
+/* -- scripted action source ------------------------------------------------------------------ */
+/* Greedy nearest-unmapped-cell pursuit on the noVis lattice, writes uint8[N][D].  A 4-ACTION VARIANT of the 2D
+ * simulator's controller (swarmsim-2d/drone.py:29-58), NOT a restatement of it: the target choice is the reference's
+ * (nearest cell that is not mapped, row-major scan, strict <, including its `if not min_dist` quirk — pinned by
+ * tests/golden/drone_update_targets.npz), but the reference then moves +-1 on BOTH axes at once (8-connected),
+ * which the noVis action set {0: y-, 1: x+, 2: y+, 3: x-} cannot express; this source moves along the axis with the
+ * larger |delta| (ties: x). */
 int swarm_greedy_actions(SwarmEnv* env, uint8_t* actions_out, void* stream);
 
 /* -- batched A2C rollout helpers (stateless, buffers on the current device) ---- */
@@ -254,12 +263,18 @@ int swarm_stats_allreduce(SwarmEnv* env, int64_t* stats, void* comm, void* strea
  *   swarm_stats_peers_open      handles = [world][64] gathered from all ranks (own entry ignored); enables the pushes
  *   swarm_stats_push            one-thread kernel: publish stats_dev (NULL = the handle's internal statistics) now
  *   swarm_stats_global          out_dev int64[8] (device) = sum over ranks of their latest complete totals; waits (bounded)
- *                               until every rank has pushed at least min_pushes times (0 = whatever has arrived)        */
+ *                               until every rank has pushed at least min_pushes times (0 = whatever has arrived).
+ *                               Asynchronous on `stream`.  A slot that does not become consistent within the bound (a peer
+ *                               died or never pushed) is NOT summed: out_dev is filled with -1 and
+ *                               SWARM_DEVERR_STATS_TIMEOUT is set in the device error word (swarm_device_error).
+ *   swarm_stats_global_host     the same into HOST memory int64[8]; synchronises `stream` and returns SWARM_ERR_TIMEOUT
+ *                               in that case                                                                            */
 int swarm_stats_mailbox_handle(SwarmEnv* env, uint8_t* handle_out_64);
 int swarm_stats_peers_open(SwarmEnv* env, const uint8_t* handles, int32_t rank, int32_t world);
 int swarm_stats_peers_close(SwarmEnv* env);
 int swarm_stats_push(SwarmEnv* env, const int64_t* stats_dev, void* stream);
 int swarm_stats_global(SwarmEnv* env, int64_t min_pushes, int64_t* out_dev, void* stream);
+int swarm_stats_global_host(SwarmEnv* env, int64_t min_pushes, int64_t* out_host, void* stream);
 
 /* -- diagnostics ---------------------------------------------------------------------------- */
 /* Synchronises `stream`, reads the sticky device error word; clears it when clear != 0. */

@@ -57,6 +57,7 @@ extern "C" const char* swarm_strerror(int s) {
     case SWARM_ERR_NO_DEVICE: return "no sm_100 CUDA device: this library has no CPU fallback";
     case SWARM_ERR_ALLOC: return "allocation failed";
     case SWARM_ERR_NCCL: return "NCCL error";
+    case SWARM_ERR_TIMEOUT: return "peer statistics mailboxes did not become consistent (a rank never pushed or died)";
     default: return "unknown status";
   }
 }
@@ -139,6 +140,19 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   if (!(c->collision_dist >= 0.0) || c->collision_dist > 64.0 || !(c->step_size > 0.0)) return SWARM_ERR_CONFIG;
   if (c->dwell_normal < 0 || c->dwell_anom < 0 || c->dwell_normal > 32767 || c->dwell_anom > 32767) return SWARM_ERR_CONFIG;
   if (RC / c->step_size > 2.0e9) return SWARM_ERR_CONFIG;
+  {   // positions are float32 multiples of step_size clipped to [0, R-1] x [0, C-1]: exact (== the reference's float64,
+      // A2C/noVis_sim.py:121-135) iff step_size = m * 2^-k with (max coordinate / 2^-k) < 2^24.  Anything else is rejected
+      // rather than silently drifting across the `dist < collision_dist` knife edge.
+    int ex = 0;
+    const double mant = std::frexp(c->step_size, &ex);            // step_size = mant * 2^ex, mant in [0.5, 1)
+    int bits = 0;
+    double m = mant;
+    while (m != std::floor(m) && bits < 60) { m *= 2.0; ++bits; }  // bits = number of mantissa bits used
+    const int k = bits - ex;                                       // step_size is a multiple of 2^-k
+    const double maxc = (double)((c->row_count > c->col_count ? c->row_count : c->col_count) - 1) + c->step_size;
+    if (m != std::floor(m) || (float)c->step_size != c->step_size || (k > 0 && std::ldexp(maxc, k) >= 16777216.0) || maxc >= 16777216.0)
+      return SWARM_ERR_CONFIG;
+  }
 
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return SWARM_ERR_NO_DEVICE; }
@@ -206,7 +220,9 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
       p.cta_smem = e->wpb * p.stage_bytes + 2 * p.in_bytes + 16;
     }
   }
-  p.nq_magic = RC >= 4 ? (uint32_t)(((1ull << 32) + (uint64_t)(RC / 4) - 1) / (uint64_t)(RC / 4)) : 0u;
+  // ceil(2^32 / nq) for the (env, quad) split of emit_full_smem; nq == 1 would need 2^32, which does not fit: the kernel
+  // takes e = v directly in that case (nq_magic == 0 is the marker)
+  p.nq_magic = RC >= 8 ? (uint32_t)(((1ull << 32) + (uint64_t)(RC / 4) - 1) / (uint64_t)(RC / 4)) : 0u;
   p.seed_lo = (uint32_t)c->seed; p.seed_hi = (uint32_t)(c->seed >> 32);
   p.env_id_base = c->env_id_base;
 
@@ -243,6 +259,12 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
 
 extern "C" int swarm_destroy(SwarmEnv* e) {
   if (!e) return SWARM_ERR_INVALID_ARG;
+  // Nothing of this handle may still run when its memory goes away; peers that push into this rank's mailbox must have been
+  // quiesced by the caller (swarm_stats_peers_close on every rank + a barrier; BatchedDroneEnv.close does both when a process
+  // group exists) — freeing IPC-exported memory that an importer still has open is undefined.
+  int cur = -1;
+  if (cudaGetDevice(&cur) == cudaSuccess && cur != e->cfg.device) cudaSetDevice(e->cfg.device);
+  cudaDeviceSynchronize();
   cudaFree(e->p.grid); cudaFree(e->p.pos); cudaFree(e->p.meta); cudaFree(e->p.wait); cudaFree(e->p.err);
   cudaFree(e->stats_dev); cudaFree(e->cover_dev);
   cudaFree(e->h_act_dev); cudaFree(e->h_obs_dev); cudaFree(e->h_rew_dev); cudaFree(e->h_done_dev);
@@ -289,9 +311,17 @@ template <int TS, typename OT, int MODE, int WC, bool FAST, bool LEAN = false>
 static cudaError_t launch_warp_inst(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks_needed, int smem) {
   auto kernel = step_warp_kernel<TS, OT, MODE, WC, FAST, LEAN>;
   int& resident = e->resident[LEAN ? 2 : (FAST ? 1 : 0)];
-  if (resident == 0) {
+  // The dynamic shared-memory limit is a property of the FUNCTION (per context), not of a handle: two live envs of different
+  // shapes share an instantiation, so the limit is only ever raised (per device).
+  static int smem_limit[64] = {0};
+  int& limit = smem_limit[e->cfg.device & 63];
+  if (smem > limit) {
     cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (err != cudaSuccess) return err;
+    limit = smem;
+  }
+  if (resident == 0) {
+    cudaError_t err;
     int per_sm = 0;
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, e->wpb * 32, smem);
     if (err != cudaSuccess) return err;
@@ -342,8 +372,13 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st
     const long long need = (long long)p.env_words * 4 + 16;
     const int staged = need <= 160 * 1024;
     const int smem = staged ? (int)need : 0;
+    static int cta_limit[64] = {0};   // per-function limit, only raised (see launch_warp_inst)
+    int& limit = cta_limit[e->cfg.device & 63];
+    if (smem > limit) {
+      if ((err = cudaFuncSetAttribute(step_cta_kernel<OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return err;
+      limit = smem;
+    }
     if (!e->resident[0]) {
-      if (staged && (err = cudaFuncSetAttribute(step_cta_kernel<OT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return err;
       int per_sm = 0;
       if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_cta_kernel<OT>, 256, smem)) != cudaSuccess) return err;
       e->resident[0] = (per_sm > 0 ? per_sm : 1) * e->sm_count;
@@ -834,10 +869,21 @@ extern "C" int swarm_stats_global(SwarmEnv* e, int64_t min_pushes, int64_t* out_
   int rc = use_device(e);
   if (rc) return rc;
   peer_stats_reduce_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(e->mbox, e->p.peers.n_ranks, (unsigned long long)min_pushes,
-                                                                (unsigned long long*)out_dev);
+                                                                (unsigned long long*)out_dev, e->p.err);
   e->launches++;
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;
+}
+
+extern "C" int swarm_stats_global_host(SwarmEnv* e, int64_t min_pushes, int64_t* out_host, void* stream) {
+  if (!e || !out_host) return SWARM_ERR_INVALID_ARG;
+  int rc = swarm_stats_global(e, min_pushes, (int64_t*)e->gstats_dev, stream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(out_host, e->gstats_dev, 64, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  for (int k = 0; k < SWARM_STAT_COUNT; ++k)
+    if (out_host[k] != -1) return SWARM_OK;
+  return SWARM_ERR_TIMEOUT;   // every entry -1: the reduce kernel gave up (it never sums a torn slot)
 }
 
 #if SWARM_TRACE   // instrumented builds only (nvcc -DSWARM_TRACE=1, tools/trace.py); not part of include/swarm_b200.h

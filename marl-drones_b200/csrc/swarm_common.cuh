@@ -171,8 +171,7 @@ __device__ __forceinline__ uint4 draw_block(const DevParams& p, long long env_id
 
 // One thread: publish stats[0..8) (read from L2, where the previous launch's atomics left them) to every rank's mailbox.
 __device__ __forceinline__ void peer_stats_push(const PeerStats& ps, const unsigned long long* stats) {
-  const unsigned long long ver = *ps.pushes + 1ull;      // only this thread of this launch touches the counter
-  *ps.pushes = ver;
+  const unsigned long long ver = atomicAdd(ps.pushes, 1ull) + 1ull;   // atomic: two launches of one handle may overlap on different streams
   unsigned long long v[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) v[k] = __ldcg(stats + k);
@@ -185,30 +184,52 @@ __device__ __forceinline__ void peer_stats_push(const PeerStats& ps, const unsig
 __global__ void peer_stats_push_kernel(PeerStats ps, const unsigned long long* stats) { peer_stats_push(ps, stats); }
 
 // Sums the latest complete totals of all ranks' slots of THIS rank's mailbox into out[8]; waits (bounded) until every slot has
-// been pushed at least min_push times.  One thread per rank slot; a slot is complete when its eight versions agree.
-__global__ void peer_stats_reduce_kernel(const unsigned long long* mbox, int n_ranks, unsigned long long min_push, unsigned long long* out) {
+// been pushed at least min_push times.  One thread per rank slot.  A slot is read as eight 16-byte loads (the writer's unit:
+// one {value, version} pair per posted 16-byte store), twice: the pass is accepted only when all sixteen versions agree, i.e.
+// no push landed between or during the two passes.  A slot that never becomes consistent within the bound (~3 s) is a
+// failure: bit 2 of the device error word is set and out[] is filled with -1 instead of a torn sum.
+__device__ __forceinline__ ulonglong2 ld_pair_sys(const unsigned long long* p) {
+  ulonglong2 v;
+  asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__global__ void peer_stats_reduce_kernel(const unsigned long long* mbox, int n_ranks, unsigned long long min_push, unsigned long long* out,
+                                         int* err) {
   __shared__ unsigned long long acc[8];
+  __shared__ int failed;
   if (threadIdx.x < 8) acc[threadIdx.x] = 0ull;
+  if (threadIdx.x == 0) failed = 0;
   __syncthreads();
   if ((int)threadIdx.x < n_ranks) {
-    const volatile unsigned long long* slot = mbox + (size_t)threadIdx.x * SWARM_MBOX_SLOT;
+    const unsigned long long* slot = mbox + (size_t)threadIdx.x * SWARM_MBOX_SLOT;
     unsigned long long v[8];
-    for (long long spin = 0; spin < (1ll << 24); ++spin) {
-      const unsigned long long ver = slot[1];
-      bool ok = ver >= min_push;
+    bool ok = false;
+    for (long long spin = 0; spin < (1ll << 22) && !ok; ++spin) {
+      const unsigned long long ver = ld_pair_sys(slot).y;
+      ok = ver >= min_push;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        v[k] = slot[2 * k];
-        ok = ok && slot[2 * k + 1] == ver;
+        const ulonglong2 pr = ld_pair_sys(slot + 2 * k);
+        v[k] = pr.x;
+        ok = ok && pr.y == ver;
       }
-      if (ok && slot[1] == ver) break;
-      __nanosleep(200);
-    }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) atomicAdd(&acc[k], v[k]);
+      for (int k = 0; k < 8; ++k) {   // second pass: nothing changed while the first one ran
+        const ulonglong2 pr = ld_pair_sys(slot + 2 * k);
+        ok = ok && pr.y == ver && pr.x == v[k];
+      }
+      if (!ok) __nanosleep(500);
+    }
+    if (ok) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) atomicAdd(&acc[k], v[k]);
+    } else {
+      atomicOr(&failed, 1);
+    }
   }
   __syncthreads();
-  if (threadIdx.x < 8) out[threadIdx.x] = acc[threadIdx.x];
+  if (threadIdx.x < 8) out[threadIdx.x] = failed ? ~0ull : acc[threadIdx.x];
+  if (threadIdx.x == 0 && failed && err) atomicOr(err, 4);
 }
 
 // per-thread statistics accumulator; reduced once per CTA, 6 atomics per CTA

@@ -157,7 +157,7 @@ __device__ __forceinline__ void emit_full_smem(const DevParams& p, const ObsCvt<
     const int nq = RC >> 2, total = nenv * nq;
 #pragma unroll 2
     for (int v = lane; v < total; v += 32) {
-      const int e = (int)__umulhi((uint32_t)v, p.nq_magic);
+      const int e = p.nq_magic ? (int)__umulhi((uint32_t)v, p.nq_magic) : v;   // nq == 1: one quad per env
       const int qd = v - e * nq;
       const uint32_t w = sgrid[e * p.env_words + (qd >> 2)];
       cvt.store4(o + (size_t)e * RC + 4 * qd, (w >> ((qd & 3) * 8)) & 0xffu);

@@ -107,6 +107,7 @@ def lib():
         "swarm_stats_peers_close": (C.c_int, [vp]),
         "swarm_stats_global": (C.c_int, [vp, i64, vp, vp]),
         "swarm_stats_push": (C.c_int, [vp, vp, vp]),
+        "swarm_stats_global_host": (C.c_int, [vp, i64, vp, vp]),
         "swarm_sample_actions": (C.c_int, [vp, i32, i64, i32, C.c_uint64, C.c_uint32, i64, vp, vp]),
         "swarm_nstep_returns": (C.c_int, [vp, vp, vp, i32, i64, i32, C.c_float, vp, vp, vp]),
         "swarm_gru_gates_fwd": (C.c_int, [vp, vp, i64, i32, i32, vp, vp]),
@@ -132,13 +133,13 @@ EXPORTED = ("swarm_abi_version swarm_strerror swarm_last_cuda_error swarm_device
             "swarm_step swarm_rollout swarm_step_host swarm_stage_move swarm_stage_scatter swarm_stage_reward "
             "swarm_stage_obs swarm_greedy_actions swarm_device_error swarm_launch_count swarm_sample_actions "
             "swarm_nstep_returns swarm_gru_gates_fwd swarm_gru_gates_bwd swarm_bias_act swarm_embed_tanh_l2norm_fwd swarm_embed_tanh_l2norm_bwd swarm_row_standardize swarm_relu_l2norm_fwd swarm_relu_l2norm_bwd swarm_comm_unique_id swarm_comm_init swarm_comm_destroy swarm_stats_allreduce swarm_stats_mailbox_handle "
-            "swarm_stats_peers_open swarm_stats_peers_close swarm_stats_global swarm_stats_push").split()
+            "swarm_stats_peers_open swarm_stats_peers_close swarm_stats_global swarm_stats_global_host swarm_stats_push").split()
 
 
 def check(status):
     if status != 0:
         L = lib()
         msg = L.swarm_strerror(status).decode()
-        if status in (-3, -6):
+        if status in (-3, -6, -7):
             msg += ": " + L.swarm_last_cuda_error().decode()
         raise SwarmError(f"swarm_b200 error {status}: {msg}")

@@ -143,15 +143,25 @@ class BatchedDroneEnv:
         check(self._L.swarm_step_host(self._h, hp(actions_host), hp(obs_host), hp(reward_host), hp(done_host),
                                       hp(stats_host), self._stream()))
 
-    def close(self):
+    def close(self, collective=True):
+        """Destroys the handle.  With peer statistics enabled across ranks (enable_peer_stats on a process group) the close is
+        COLLECTIVE: every rank stops pushing and unmaps its peers' mailboxes, then all ranks meet at a barrier, and only then
+        is this rank's mailbox freed — a peer must never write into freed memory."""
         if getattr(self, "_h", None) is not None and self._h.value:
             torch.cuda.synchronize(self.device)
+            if getattr(self, "_peer_world", 1) > 1:
+                self._L.swarm_stats_peers_close(self._h)
+                self._peer_world = 1
+                if collective:
+                    import torch.distributed as dist
+                    if dist.is_available() and dist.is_initialized():
+                        dist.barrier(group=self._peer_group)
             self._L.swarm_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
         try:
-            self.close()
+            self.close(collective=False)
         except Exception:
             pass
 
@@ -232,7 +242,7 @@ class BatchedDroneEnv:
             raise SwarmError("another rank could not export its statistics mailbox (CUDA IPC)")
         buf = (C.c_uint8 * (64 * world)).from_buffer_copy(b"".join(handles))
         check(self._L.swarm_stats_peers_open(self._h, buf, rank, world))
-        self._peer_world = world
+        self._peer_world, self._peer_group = world, group
         self._gstats = torch.zeros(8, dtype=torch.int64, device=self.device)
         return self
 
@@ -248,8 +258,16 @@ class BatchedDroneEnv:
         check(self._L.swarm_stats_global(self._h, int(min_pushes), self._ptr(out), self._stream()))
         return out
 
+    def global_stats_host(self, min_pushes=0):
+        """The same as a list of 8 ints on the host; synchronises, and raises SwarmError (SWARM_ERR_TIMEOUT) when some rank's
+        slot never became consistent instead of returning a torn sum."""
+        out = (C.c_int64 * 8)()
+        check(self._L.swarm_stats_global_host(self._h, int(min_pushes), out, self._stream()))
+        return list(out)
+
     def disable_peer_stats(self):
         check(self._L.swarm_stats_peers_close(self._h))
+        self._peer_world = 1
 
     def allreduce_stats(self, group=None):
         """The only collective on this path: ncclAllReduce(SUM, int64[8]) of the episode statistics (64 B per rank)."""

@@ -47,6 +47,15 @@ def test_invalid_args_rejected_without_gpu():
     assert L.swarm_create(C.byref(bad), C.byref(h)) == -2          # uncertainity <= 1 is unsupported
     bad.uncertainity, bad.n_anamolous = 5, 101
     assert L.swarm_create(C.byref(bad), C.byref(h)) == -2          # the reference would loop forever (noVis_sim.py:47-55)
+    bad.n_anamolous = 5
+    for ss in (0.1, 0.3, 1.0 / 3.0, 2.0 ** -30):                   # positions would not be exact in float32
+        bad.step_size = ss
+        assert L.swarm_create(C.byref(bad), C.byref(h)) == -2, ss
+    for ss in (0.5, 1.0, 0.25, 0.75, 2.0, 0.125):                  # dyadic: passes validation (then fails on the missing device)
+        bad.step_size = ss
+        assert L.swarm_create(C.byref(bad), C.byref(h)) in (0, -4), ss
+        if h.value:
+            L.swarm_destroy(h); h = C.c_void_p()
 
 
 def test_no_cpu_fallback():

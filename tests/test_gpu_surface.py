@@ -248,3 +248,56 @@ def test_lean_and_generic_kernels_agree(cfg):
     ga, gb = a.get_state(), b.get_state()
     assert all(torch.equal(x, y) for x, y in zip(ga[:3], gb[:3])) and torch.equal(a.stats, b.stats)
     a.close(); b.close()
+
+
+def test_two_live_envs_of_one_instantiation_keep_their_shared_memory_limit():
+    """the dynamic shared-memory limit belongs to the kernel function, not to a handle.  Env A (large slice) steps,
+    env B (same instantiation, smaller slice) takes its first step, then A steps again — A's launch must still be accepted."""
+    from test_gpu_parity import make_pair, run_lockstep
+    big = dict(row_count=64, col_count=64, n_drones=16, step_size=1.0, obs_mode=1, window=5)
+    small = dict(row_count=16, col_count=16, n_drones=16, step_size=1.0, obs_mode=1, window=5)
+    ga, oa = make_pair(64, auto_reset=True, seed=5, **big)
+    run_lockstep(ga, oa, 4, seed=1)
+    gb, ob = make_pair(64, auto_reset=True, seed=6, **small)
+    run_lockstep(gb, ob, 4, seed=2)
+    run_lockstep(ga, oa, 4, seed=3)          # A again, after B's first launch
+    run_lockstep(gb, ob, 4, seed=4)
+    for a, b in ((dict(row_count=32, col_count=32, n_drones=4, step_size=1.0), dict(row_count=8, col_count=8, n_drones=4, step_size=1.0)),
+                 (dict(row_count=256, col_count=256, n_drones=64, step_size=1.0), dict(row_count=40, col_count=40, n_drones=64, step_size=1.0))):
+        g1, o1 = make_pair(48, auto_reset=True, seed=7, **a)
+        run_lockstep(g1, o1, 3, seed=1)
+        g2, o2 = make_pair(48, auto_reset=True, seed=8, **b)
+        run_lockstep(g2, o2, 3, seed=2)
+        run_lockstep(g1, o1, 3, seed=3)
+        g1.close(); g2.close()
+    ga.close(); gb.close()
+
+
+@pytest.mark.parametrize("kw", [dict(row_count=2, col_count=2, n_drones=2, n_anamolous=1, step_size=1.0),
+                                dict(row_count=1, col_count=4, n_drones=3, n_anamolous=1, step_size=1.0),
+                                dict(row_count=4, col_count=1, n_drones=1, n_anamolous=0, step_size=0.5),
+                                dict(row_count=2, col_count=3, n_drones=5, n_anamolous=2, step_size=1.0)])
+def test_tiny_grids_full_obs(kw):
+    """R*C == 4 made the (env, quad) magic divisor overflow, so every env after the first of a warp group read
+    the wrong words.  2x2 / 1x4 / 4x1 (and a 6-cell grid) against the oracle, many envs per warp."""
+    from test_gpu_parity import make_pair, run_lockstep
+    g, o = make_pair(77, auto_reset=True, seed=13, **kw)
+    run_lockstep(g, o, 60, seed=5)
+    g.close()
+
+
+def test_stats_timeout_is_reported_not_summed():
+    """VERDICT r1 / ADVICE r1: a mailbox slot that never becomes consistent must surface as an error, not as a torn sum."""
+    from swarm_b200 import BatchedDroneEnv, SwarmError
+    env = BatchedDroneEnv(64, row_count=8, col_count=8, n_drones=4, step_size=1.0, auto_reset=True, seed=1).enable_peer_stats()
+    env.step(torch.zeros((64, 4), dtype=torch.uint8, device=env.device))
+    env.push_stats()
+    assert env.global_stats_host(min_pushes=1)[0] == 64
+    with pytest.raises(SwarmError, match="consistent"):
+        env.global_stats_host(min_pushes=10 ** 9)        # nobody will ever push that often: bounded wait, then an error
+    assert env.device_error() & 4
+    g = env.global_stats(min_pushes=10 ** 9)
+    torch.cuda.synchronize()
+    assert g.tolist() == [-1] * 8
+    assert env.device_error() & 4
+    env.close()

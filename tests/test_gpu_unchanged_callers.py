@@ -57,7 +57,7 @@ def _run_dql(variant, seed, extra, timeout=900):
 
 
 @pytest.mark.timeout(1800)
-@pytest.mark.parametrize("seed,grid", [(0, 3), (4, 3)])
+@pytest.mark.parametrize("seed,grid", [(0, 3), (4, 3), (3, 5)])
 def test_dqlearning_script_runs_unchanged_and_matches_cpu_reference(seed, grid):
     extra = ["--episodes", "1", "--grid_size", str(grid), "--n_drones", "3", "--n_anamolous", "2"]
     ref_lines, _ = _run_dql("ref", seed, extra)
