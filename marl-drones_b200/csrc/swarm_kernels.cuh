@@ -107,7 +107,13 @@ __global__ void __launch_bounds__(256) move_kernel(const __grid_constant__ DevPa
   }
 }
 
-// Scripted greedy controller on the noVis lattice (restates swarmsim-2d/drone.py:29-58; see oracle_greedy_actions).
+// Scripted greedy action source on the noVis lattice.  The TARGET is the 2D simulator's (Drone.update,
+// swarmsim-2d/drone.py:29-47; oracle: drone_update_target, pinned by tests/golden/drone_update_targets.npz): row-major scan,
+// mapped cells skipped, strict `min_dist > dist`, and the `if not min_dist` quirk — a running minimum of exactly 0.0 counts as
+// "no minimum yet", so the next unmapped cell in scan order replaces it unconditionally.  The MOVE is a 4-action variant (the
+// reference steps +-1 on both axes at once, which the noVis action set cannot express): the axis with the larger |delta|.
+// Distances: the reference compares ((dx)**2 + (dy)**2) ** 0.5; on the lattice (multiples of 2^-k) the squares are exact and
+// sqrt is strictly monotone on them at these magnitudes, so comparing the squared distances picks the same cell.
 __global__ void __launch_bounds__(256) greedy_kernel(const __grid_constant__ DevParams p, uint8_t* actions) {
   const long long n = (long long)p.N * p.D;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -115,14 +121,15 @@ __global__ void __launch_bounds__(256) greedy_kernel(const __grid_constant__ Dev
     const uint32_t* g = p.grid + (size_t)env * p.env_words;
     const float2 q = p.pos[i];
     const double x = q.x, y = q.y;
-    double best = -1.0;
+    double best = 0.0;
+    bool have = false;
     int bx = -1, by = -1;
     for (int gx = 0; gx < p.R; ++gx)
       for (int gy = 0; gy < p.C; ++gy) {
         const int cell = gy * p.R + gx;
         if ((ld_grid(g + (cell >> 4)) >> ((cell & 15) * 2)) & 3u) {
           const double d2 = (gx - x) * (gx - x) + (gy - y) * (gy - y);
-          if (best < 0.0 || d2 < best) { best = d2; bx = gx; by = gy; }
+          if (!have || best == 0.0 || d2 < best) { have = true; best = d2; bx = gx; by = gy; }
         }
       }
     uint8_t a = 0;

@@ -59,6 +59,8 @@ def lib():
         L.oracle_reset_numpy.restype = None
         L.oracle_greedy_actions.argtypes = [C.POINTER(OracleConfig), C.c_int32, vp, vp, vp]
         L.oracle_greedy_actions.restype = None
+        L.oracle_drone_update.argtypes = [C.POINTER(OracleConfig), C.c_int32, vp, vp, vp, vp]
+        L.oracle_drone_update.restype = None
         L.oracle_philox4x32_10.argtypes = [vp, vp, vp]
         L.oracle_philox4x32_10.restype = None
         L.oracle_max_threads.restype = C.c_int
@@ -133,6 +135,14 @@ class OracleBatch:
         out = np.empty((self.N, self.D), np.uint8)
         lib().oracle_greedy_actions(C.byref(self.cfg), self.N, _p(self.grid), _p(self.pos), _p(out))
         return out
+
+
+    def drone_update(self):
+        """(target int32 [N, D] flat cell or -1, dir int8 [N, D, 2]) of swarmsim-2d/drone.py:29-59 on the lattice."""
+        target = np.empty((self.N, self.D), np.int32)
+        direction = np.empty((self.N, self.D, 2), np.int8)
+        lib().oracle_drone_update(C.byref(self.cfg), self.N, _p(self.grid), _p(self.pos), _p(target), _p(direction))
+        return target, direction
 
 
 def philox(ctr, key):

@@ -15,7 +15,9 @@
  *   _drone_dist         A2C/noVis_sim.py:92-102
  *   obs                 A2C/noVis_sim.py:168-170 (grid.T.flatten)
  *   auto-reset on done  A2C/envs.py:22-26
- *   dwell counters      swarmsim-2d/goals.py:4-41 + run_env.py:183-201 (parity unpinned)
+ *   dwell counters      swarmsim-2d/goals.py:4-41 + run_env.py:183-201 (the counter semantics are
+ *                                                 pinned by tests/golden/goals_dwell.npz, frozen from the unmodified goals.py)
+ *   greedy target       swarmsim-2d/drone.py:29-47 (pinned by tests/golden/drone_update_targets.npz)
  *   window obs          SURVEY App. B.1 (ours; parity unpinned)
  *
  * Parity pin: tests/test_oracle_vs_reference.py drives this file and the live reference with the
@@ -316,26 +318,69 @@ void oracle_emit_obs_batch(const OracleConfig* cfg, int32_t N, const int8_t* gri
   for (int32_t n = 0; n < N; ++n) oracle_emit_obs(cfg, grid_t + n * RC, pos + (size_t)n * D * 2, obs + (size_t)n * obs_per_env);
 }
 
-/* Scripted greedy controller on the noVis lattice (restates swarmsim-2d/drone.py:29-58; parity unpinned):
- * target = nearest cell with grid > 0 (strict <, first in x-major scan on ties); the drone takes the axis
- * with the larger |delta| (x on ties): x+ -> 1, x- -> 3, y+ -> 2, y- -> 0; action 0 when nothing is left
- * or when it already sits on the target. */
+/* Target choice of the 2D simulator's scripted controller, Drone.update (swarmsim-2d/drone.py:29-47), on the noVis
+ * lattice: row-major scan (row == x outer, col == y inner), cells that are mapped are skipped (`grid == -1` there,
+ * `grid == 0` here), the distance is `((dx)**2 + (dy)**2) ** 0.5` compared with a strict `min_dist > dist`, and the
+ * QUIRK of `if not min_dist:` — Python truthiness: it fires when min_dist is None AND when the running minimum is
+ * exactly 0.0, so after a cell at distance 0 the NEXT unmapped cell in scan order replaces it unconditionally.
+ * Returns the flat target cell gy*R + gx, or -1 when nothing is left (the reference returns 1, drone.py:49-50).
+ * Pinned by tests/golden/drone_update_targets.npz (frozen from the unmodified drone.py, tests/golden/make_donor_golden.py). */
+static int drone_update_target(const OracleConfig* cfg, const int8_t* g, double x, double y) {
+  const int R = cfg->row_count, C = cfg->col_count;
+  int have = 0, target = -1;
+  double min_dist = 0.0;
+  for (int gx = 0; gx < R; ++gx)
+    for (int gy = 0; gy < C; ++gy) {
+      if (g[gy * R + gx] <= 0) continue;                                  /* drone.py:34-35 */
+      const double dist = pow((x - gx) * (x - gx) + (y - gy) * (y - gy), 0.5);   /* drone.py:26-27 */
+      if (!have || min_dist == 0.0) {                                     /* `if not min_dist` drone.py:39-42 */
+        have = 1; min_dist = dist; target = gy * R + gx;
+        continue;
+      }
+      if (min_dist > dist) { min_dist = dist; target = gy * R + gx; }     /* drone.py:43-45 */
+    }
+  return target;
+}
+
+/* Drone.update for every drone: target[n][i] (flat cell or -1) and the reference's 8-connected move direction
+ * dir[n][i] = the net (dx, dy) of drone.py:52-59 (+-1 on EACH axis toward the target; (0, 0) when there is none). */
+void oracle_drone_update(const OracleConfig* cfg, int32_t N, const int8_t* grid_t, const double* pos, int32_t* target, int8_t* dir) {
+  const int R = cfg->row_count, C = cfg->col_count, D = cfg->n_drones;
+  for (int32_t n = 0; n < N; ++n)
+    for (int i = 0; i < D; ++i) {
+      const double x = pos[((size_t)n * D + i) * 2], y = pos[((size_t)n * D + i) * 2 + 1];
+      const int t = drone_update_target(cfg, grid_t + (size_t)n * R * C, x, y);
+      int sx = 0, sy = 0;
+      if (t >= 0) {
+        const double tx = t % R, ty = t / R;
+        /* drone.py:52-59, literally: four sequential, NON-exclusive ifs — a drone less than one unit above its target is
+         * decremented and then incremented again (net 0), which a sign() restatement gets wrong */
+        double nx = x, ny = y;
+        if (ny > ty) ny -= 1;      /* center_x <-> column <-> noVis y */
+        if (ny < ty) ny += 1;
+        if (nx > tx) nx -= 1;      /* center_y <-> row <-> noVis x */
+        if (nx < tx) nx += 1;
+        sx = (int)(nx - x); sy = (int)(ny - y);
+      }
+      if (target) target[(size_t)n * D + i] = t;
+      if (dir) { dir[((size_t)n * D + i) * 2] = (int8_t)sx; dir[((size_t)n * D + i) * 2 + 1] = (int8_t)sy; }
+    }
+}
+
+/* Scripted greedy ACTION source on the noVis lattice — a 4-action VARIANT of Drone.update, not a restatement: the target
+ * is the reference's (drone_update_target above, pinned), but the reference then moves +-1 on both axes at once, which
+ * the noVis action set cannot express; here the drone takes the axis with the larger |delta| (x on ties):
+ * x+ -> 1, x- -> 3, y+ -> 2, y- -> 0; action 0 when nothing is left or when it already sits on the target. */
 void oracle_greedy_actions(const OracleConfig* cfg, int32_t N, const int8_t* grid_t, const double* pos, uint8_t* actions) {
   const int R = cfg->row_count, C = cfg->col_count, D = cfg->n_drones;
   for (int32_t n = 0; n < N; ++n)
     for (int i = 0; i < D; ++i) {
       const int8_t* g = grid_t + (size_t)n * R * C;
       double x = pos[((size_t)n * D + i) * 2], y = pos[((size_t)n * D + i) * 2 + 1];
-      double best = -1.0; int bx = -1, by = -1;
-      for (int gx = 0; gx < R; ++gx)
-        for (int gy = 0; gy < C; ++gy)
-          if (g[gy * R + gx] > 0) {
-            double d2 = (gx - x) * (gx - x) + (gy - y) * (gy - y);
-            if (best < 0.0 || d2 < best) { best = d2; bx = gx; by = gy; }
-          }
+      const int t = drone_update_target(cfg, g, x, y);
       uint8_t a = 0;
-      if (bx >= 0) {
-        double dx = bx - x, dy = by - y;
+      if (t >= 0) {
+        double dx = (t % R) - x, dy = (t / R) - y;
         if (dx == 0.0 && dy == 0.0) a = 0;
         else if (fabs(dx) >= fabs(dy)) a = dx > 0 ? 1 : 3;
         else a = dy > 0 ? 2 : 0;
