@@ -19,6 +19,7 @@ struct SwarmEnv {
   int ts;                 // tile size (lanes per env) of the staged warp kernel
   int staged;             // 1: swarm_warp.cuh kernel (grid staged in shared memory), 0: swarm_cta.cuh (one CTA per env)
   int wpb;                // warps per block of the staged kernel
+  int dyn;                // staged kernel: dynamic CTA-group schedule (atomic counter) instead of static striding
   int resident[3];        // resident CTAs of the staged kernel on this device ([0] generic, [1] FAST, [2] LEAN instantiation); 0 = not yet queried
   int sm_count;
   long long launches;
@@ -85,26 +86,25 @@ static int stage_bytes_for(const SwarmConfig* c, int epw) {
 
 static int align16(long long v) { return (int)((v + 15) / 16 * 16); }
 
+// Per-warp shared-memory needs of the staged kernel for tile size ts: obs staging and one input stage.
+static void warp_bytes(const SwarmConfig* c, const DevParams* p, int ts, int* stage, int* in_w) {
+  const int epw = 32 / ts;
+  *stage = stage_bytes_for(c, epw);
+  *in_w = epw * (p->env_words * 4 + 16 + 16) + align16((long long)epw * c->n_drones * 8) + align16((long long)epw * c->n_drones);
+}
+
 // Smallest power-of-two tile >= D (min 4), widened while the batch would give too few warps to fill the GPU.
-// Returns 0 when the shape does not fit the staged kernel (D > 32 or the per-warp slice is too large); otherwise fills the
-// per-warp shared-memory carve-up in `p`.
+// Returns 0 when the shape does not fit the staged kernel (D > 32, PLANE-mode anomalies, or a per-warp slice too large for a
+// two-stage ring).
 static int pick_tile(const SwarmConfig* c, int sms, DevParams* p) {
-  if (c->n_drones > 32) return 0;
+  if (c->n_drones > 32 || !p->list_mode) return 0;
   int ts = 4;
   while (ts < c->n_drones) ts <<= 1;
   while (ts < 32 && (long long)c->n_envs / (32 / ts) < (long long)sms * 16) ts <<= 1;
   for (; ts <= 32; ts <<= 1) {
-    const int epw = 32 / ts;
-    const int stage = stage_bytes_for(c, epw);
-    const int gridb = epw * p->env_words * 4;
-    const int posb = align16((long long)epw * c->n_drones * 8), metab = epw * 16, actb = align16((long long)epw * c->n_drones);
-    const long long in_bytes = (long long)gridb + posb + metab + actb;
-    const long long ws = (long long)stage + 2 * in_bytes + 16;
-    if (ws <= kWarpSmemMax) {
-      p->stage_bytes = stage;
-      p->warp_smem = (int)ws;
-      return ts;
-    }
+    int stage = 0, in_w = 0;
+    warp_bytes(c, p, ts, &stage, &in_w);
+    if ((long long)stage + 2ll * in_w + 16 <= kWarpSmemMax) return ts;
   }
   return 0;
 }
@@ -178,7 +178,17 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   p.punish_thr = (int)std::floor((double)RC / c->step_size);
   p.cd_fast = c->collision_dist <= 0.5;
   p.scan_m = (int)std::ceil(c->collision_dist) + 1;
-  p.env_words = (int)(((RC + 15) / 16 + 3) / 4 * 4);
+  p.env_words = (int)(((RC + 31) / 32 + 3) / 4 * 4);
+  p.list_mode = c->n_anamolous <= 8 && c->row_count <= 256 && c->col_count <= 256;
+  {   // float32-exact coordinates: step_size = m 2^-k (validated above) with k <= 12 (squares of offsets <= 1/2 exact) and
+      // (largest coordinate in units of 2^-k)^2 * 2 <= 2^24 (squared pair distances exact)
+    int ex = 0, bits = 0;
+    double m = std::frexp(c->step_size, &ex);
+    while (m != std::floor(m) && bits < 60) { m *= 2.0; ++bits; }
+    const int k = bits - ex > 0 ? bits - ex : 0;
+    const double M = std::ldexp((double)((c->row_count > c->col_count ? c->row_count : c->col_count) - 1) + c->step_size, k);
+    p.f32_exact = k <= 12 && M <= 2896.0;
+  }
   p.obs_per_env = c->obs_mode == SWARM_OBS_FULL ? (int)RC : c->n_drones * c->window * c->window;
   p.ss = (float)c->step_size; p.xmax = (float)(c->row_count - 1); p.ymax = (float)(c->col_count - 1);
   p.cd = c->collision_dist;
@@ -192,33 +202,53 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
     while (std::sqrt(z) <= p.spread_thr) z = std::nextafter(z, INFINITY);
     while (z > 0.0 && std::sqrt(z) > p.spread_thr) z = std::nextafter(z, -INFINITY);
     p.spread2_thr = z;                               // largest z with sqrt(z) <= row_count // n_drones
+    // float versions for exactly-representable d2: d2 < cd2_thr <=> d2 < (smallest float >= cd2_thr), and
+    // d2 > spread2_thr <=> d2 > (largest float <= spread2_thr)
+    float f = (float)p.cd2_thr;
+    if ((double)f < p.cd2_thr) f = std::nextafterf(f, INFINITY);
+    p.cd2_thr_f = f;
+    f = (float)p.spread2_thr;
+    if ((double)f > p.spread2_thr) f = std::nextafterf(f, -INFINITY);
+    p.spread2_thr_f = f;
   }
   e->ts = pick_tile(c, sms, &p);
   e->staged = e->ts != 0;
   if (!e->staged) e->ts = 32;
-  {   // warps per CTA: the choice that packs most warps into an SM's 227 KB (ties -> larger CTAs), at most 32 warps (registers)
-    int best = 0;
+  if (e->staged) {
+    // CTA shape and ring depth: the (warps per CTA, stages) pair that keeps most warps resident in an SM's 227 KB (register
+    // cap: SWARM_MINB CTAs of 8 warps), then the deepest ring, then the larger CTA.  SWARM_WPB / SWARM_STAGES override.
+    int stage = 0, in_w = 0;
+    warp_bytes(c, &p, e->ts, &stage, &in_w);
+    p.stage_bytes = stage;
+    int smax = 4, wforce = 0;
+    if (const char* v = getenv("SWARM_STAGES")) { const int x = atoi(v); if (x >= 2 && x <= 6) smax = x; }
+    if (const char* v = getenv("SWARM_WPB")) { const int x = atoi(v); if (x == 2 || x == 4 || x == 8) wforce = x; }
+    const long long stat = 7 * 1024 + 1024;   // static shared memory of the kernel (LUT, pad tables, barriers) + the driver's 1 KB
+    int best_warps = -1, best_s = 0;
     e->wpb = 8;
     for (int w = 8; w >= 2; w >>= 1) {
-      long long ctas = (227 * 1024) / ((long long)w * p.warp_smem + 1024 + 4400);
-      long long warps = ctas * w;
-      if (warps > 32) warps = 32;
-      if (warps > best) { best = (int)warps; e->wpb = w; }
+      if (wforce && w != wforce) continue;
+      for (int S = smax; S >= 2; --S) {
+        const long long smem = (long long)w * stage + (long long)S * w * in_w + 64 + stat;
+        if (smem > 227 * 1024) continue;
+        long long warps = (227 * 1024) / smem * w;
+        if (warps > 24) warps = 24;
+        if (warps > best_warps || (warps == best_warps && S > best_s)) { best_warps = (int)warps; best_s = S; e->wpb = w; }
+      }
     }
-    if (const char* v = getenv("SWARM_WPB")) {   // tuning knob: force the CTA size (2, 4 or 8 warps)
-      const int w = atoi(v);
-      if (w == 2 || w == 4 || w == 8) e->wpb = w;
-    }
-    if (e->staged) {   // CTA-level input buffer for EPC = wpb * EPW envs
-      const long long epc = (long long)e->wpb * (32 / e->ts);
-      const int gridb = (int)(epc * p.env_words * 4), posb = align16(epc * c->n_drones * 8), metab = (int)(epc * 16);
-      const int actb = align16(epc * c->n_drones);
-      p.off_pos = gridb;
-      p.off_meta = gridb + posb;
-      p.off_act = gridb + posb + metab;
-      p.in_bytes = gridb + posb + metab + actb;
-      p.cta_smem = e->wpb * p.stage_bytes + 2 * p.in_bytes + 16;
-    }
+    p.n_stages = best_s > 0 ? best_s : 2;
+    const long long epc = (long long)e->wpb * (32 / e->ts);
+    const int covb = (int)(epc * p.env_words * 4), listb = (int)(epc * 16), posb = align16(epc * c->n_drones * 8), metab = (int)(epc * 16);
+    const int actb = align16(epc * c->n_drones);
+    p.off_alist = covb;
+    p.off_pos = covb + listb;
+    p.off_meta = p.off_pos + posb;
+    p.off_act = p.off_meta + metab;
+    p.in_bytes = p.off_act + actb;
+    p.warp_smem = stage + p.n_stages * in_w;
+    p.cta_smem = e->wpb * p.stage_bytes + p.n_stages * p.in_bytes + 64;
+    e->dyn = 0;
+    if (const char* v = getenv("SWARM_DYN")) e->dyn = atoi(v) != 0;
   }
   // ceil(2^32 / nq) for the (env, quad) split of emit_full_smem; nq == 1 would need 2^32, which does not fit: the kernel
   // takes e = v directly in that case (nq_magic == 0 is the marker)
@@ -229,7 +259,10 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   const size_t N = (size_t)p.N;
   cudaError_t err = cudaSuccess;
   auto alloc = [&](void** ptr, size_t bytes) { if (err == cudaSuccess) err = cudaMalloc(ptr, bytes ? bytes : 16); };
-  alloc((void**)&p.grid, N * p.env_words * sizeof(uint32_t));
+  alloc((void**)&p.cov, N * p.env_words * sizeof(uint32_t));
+  if (p.list_mode) alloc((void**)&p.alist, N * 8 * sizeof(uint16_t));
+  else alloc((void**)&p.anomp, N * p.env_words * sizeof(uint32_t));
+  alloc((void**)&p.sched, 16);
   alloc((void**)&p.pos, N * p.D * sizeof(float2));
   alloc((void**)&p.meta, N * sizeof(int4));
   if (p.has_wait) alloc((void**)&p.wait, N * RC * sizeof(int16_t));
@@ -242,6 +275,7 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
     return SWARM_ERR_ALLOC;
   }
   cudaMemsetAsync(p.err, 0, 16, 0);
+  cudaMemsetAsync(p.sched, 0, 16, 0);
   cudaMemsetAsync(e->stats_dev, 0, 64, 0);
   cudaMemsetAsync(p.meta, 0, N * sizeof(int4), 0);
   reset_kernel<<<grid_blocks(e, p.N), 256, 0, 0>>>(p, nullptr, 0);
@@ -265,7 +299,7 @@ extern "C" int swarm_destroy(SwarmEnv* e) {
   int cur = -1;
   if (cudaGetDevice(&cur) == cudaSuccess && cur != e->cfg.device) cudaSetDevice(e->cfg.device);
   cudaDeviceSynchronize();
-  cudaFree(e->p.grid); cudaFree(e->p.pos); cudaFree(e->p.meta); cudaFree(e->p.wait); cudaFree(e->p.err);
+  cudaFree(e->p.cov); cudaFree(e->p.anomp); cudaFree(e->p.alist); cudaFree(e->p.sched); cudaFree(e->p.pos); cudaFree(e->p.meta); cudaFree(e->p.wait); cudaFree(e->p.err);
   cudaFree(e->stats_dev); cudaFree(e->cover_dev);
   cudaFree(e->h_act_dev); cudaFree(e->h_obs_dev); cudaFree(e->h_rew_dev); cudaFree(e->h_done_dev);
   for (int r = 0; r < SWARM_MAX_RANKS; ++r)
@@ -294,7 +328,7 @@ extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* 
   switch (which) {
     case 0: ptr = e->p.pos; b = (int64_t)(N * e->p.D * sizeof(float2)); break;
     case 1: ptr = e->p.meta; b = (int64_t)(N * sizeof(int4)); break;
-    case 2: ptr = e->p.grid; b = (int64_t)(N * e->p.env_words * 4); break;
+    case 2: ptr = e->p.cov; b = (int64_t)(N * e->p.env_words * 4); break;
     case 3: ptr = e->p.err; b = 4; break;
     case 4: ptr = e->stats_dev; b = 64; break;
     default: return SWARM_ERR_INVALID_ARG;
@@ -336,7 +370,7 @@ template <int TS, typename OT>
 static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks, int smem) {
   const DevParams& p = e->p;
   // FAST: every stage in one pass, uint8 actions, cd <= 0.5, no dwell — the swarm_step / swarm_rollout production path
-  const bool fast = (io.flags & F_ALL) == F_ALL && io.act_dtype == SWARM_ACT_U8 && p.cd_fast && !p.has_wait;
+  const bool fast = (io.flags & F_ALL) == F_ALL && io.act_dtype == SWARM_ACT_U8 && p.cd_fast && !p.has_wait && p.f32_exact;
   // LEAN: the FAST kernel with the tail / rollout / alignment bookkeeping folded away (see step_warp_kernel)
   const int epc = e->wpb * (32 / TS);
   const bool lean = fast && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epc == 0 &&
@@ -353,8 +387,10 @@ static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st
 }
 
 template <typename OT>
-static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
+static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io_in, cudaStream_t st) {
   const DevParams& p = e->p;
+  StepIO io = io_in;
+  io.dyn = e->staged ? e->dyn : 0;
   cudaError_t err = cudaSuccess;
   if (e->staged) {
     const int epw = 32 / e->ts;
@@ -369,7 +405,7 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io, cudaStream_t st
     }
   } else {
     // one CTA per env; the env's packed grid is staged in shared memory when it fits (160 KB = 640k cells)
-    const long long need = (long long)p.env_words * 4 + 16;
+    const long long need = (long long)p.env_words * 4 * (p.list_mode ? 1 : 2) + 64;
     const int staged = need <= 160 * 1024;
     const int smem = staged ? (int)need : 0;
     static int cta_limit[64] = {0};   // per-function limit, only raised (see launch_warp_inst)

@@ -1,13 +1,18 @@
 // swarm_common.cuh — device-side parameter block and small helpers shared by every kernel.
 //
 // Resident layout in HBM (struct-of-arrays, one handle per GPU):
-//   grid  uint32 [N][env_words]   2 bits per cell, 16 cells per word, flat cell index c = y*R + x
-//                                 (the reference's obs order, A2C/noVis_sim.py:168-170);
-//                                 codes: 0 mapped (value 0), 1 normal (value 1), 2 anomalous (value U); cells
-//                                 past R*C in the last word are 0.  env_words is a multiple of 4 (16 B).
+//   cov   uint32 [N][env_words]   COVERAGE MAP, 1 bit per cell, 32 cells per word, flat cell index c = y*R + x (the
+//                                 reference's obs order, A2C/noVis_sim.py:168-170): bit = 1 <=> the cell is still unmapped
+//                                 (reference grid value > 0).  Bits past R*C are 0.  env_words is a multiple of 4 (16 B).
+//   alist uint16 [N][8]           LIST mode (n_anamolous <= 8 and R, C <= 256 — every reference call site): the env's
+//                                 anomalous cells as x | y << 8, entries >= n_anamolous unused.  Static within an episode:
+//                                 a cell's value is  bit ? (listed ? U : 1) : 0, so "anomaly found" is the cleared bit.
+//   anomp uint32 [N][env_words]   PLANE mode (anything else): the anomalous cells as a second bit plane (static per episode).
 //   pos   float2 [N][D]           (x, y) = reference n_drones_pos[i]
 //   meta  int4   [N]              {step_func_count, remaining (#cells > 0), episode_return, episode}
 //   wait  int16  [N][R*C]         dwell counters, only allocated when dwell_normal|dwell_anom != 0
+// Round 1 kept 2 bits per cell; the 1-bit map halves the largest input stream of the step (cfg3: 64 -> 32 MiB per launch)
+// and the shared-memory footprint of a staged env, which is what buys the deeper TMA ring of swarm_warp.cuh.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -39,7 +44,13 @@ struct DevParams {
   int punish_thr;     // floor(R*C / step_size): punish <=> step_func_count > punish_thr   (noVis_sim.py:141-143)
   int cd_fast;        // collision_dist <= 0.5: at most one lattice cell can be hit
   int scan_m;         // ceil(cd) + 1: half-width of the bounded scan window for cd > 0.5
-  int env_words;      // uint32 words per env in the packed grid
+  int env_words;      // uint32 words per env of ONE bit plane (multiple of 4)
+  int list_mode;      // 1: anomalies in `alist` (x | y << 8, n_anom <= 8, R, C <= 256); 0: second bit plane `anomp`
+  int f32_exact;      // positions / squared distances are exact in float32 (step_size = m 2^-k, k <= 12, coordinates small):
+                      // the FAST kernels compare in float; otherwise the generic double path runs
+  float cd2_thr_f;    // smallest float >= cd2_thr:  d2 < cd2_thr <=> d2 < cd2_thr_f   for every d2 that is exactly a float
+  float spread2_thr_f;// largest float <= spread2_thr: d2 > spread2_thr <=> d2 > spread2_thr_f   likewise
+  int n_stages;       // depth of the CTA input ring of the staged kernel (TMA stages in flight)
   int obs_per_env;    // R*C or D*W*W
   float ss, xmax, ymax;
   double cd;          // collision_dist
@@ -48,17 +59,20 @@ struct DevParams {
   double spread2_thr; // largest double z with sqrt(z) <= spread_thr: sqrt(d2) > thr <=> d2 > spread2_thr
   // warp-autonomous staged kernel (swarm_warp.cuh): per-warp shared-memory carve-up, bytes
   int stage_bytes;    // obs staging (WINDOW mode), multiple of 16, >= 16
-  int in_bytes;       // one CTA input buffer for EPC = wpb*EPW envs: [grid EPC*env_words*4][pos EPC*D*8][meta EPC*16][actions EPC*D],
-                      // each part 16 B aligned
-  int off_pos, off_meta, off_act;   // byte offsets inside an input buffer
+  int in_bytes;       // one CTA input stage for EPC = wpb*EPW envs: [cov EPC*env_words*4][alist EPC*16][pos EPC*D*8][meta EPC*16]
+                      // [actions EPC*D], each part 16 B aligned
+  int off_alist, off_pos, off_meta, off_act;   // byte offsets inside an input stage
   int warp_smem;      // per-warp footprint used to size the CTA (stage_bytes + 2 * per-warp inputs + slack)
-  int cta_smem;       // dynamic shared memory of a CTA: wpb * stage_bytes + 2 * in_bytes + 16
+  int cta_smem;       // dynamic shared memory of a CTA: wpb * stage_bytes + n_stages * in_bytes + slack
   uint32_t nq_magic;  // ceil(2^32 / (RC/4)) for the FULL-mode vector -> (env, quad) split
   uint32_t seed_lo, seed_hi;
   long long env_id_base;
   // resident state
   PeerStats peers;
-  uint32_t* grid;
+  uint32_t* cov;      // coverage bit plane
+  uint32_t* anomp;    // anomaly bit plane (PLANE mode) or null
+  uint16_t* alist;    // anomaly list (LIST mode) or null
+  int* sched;         // int[4] dynamic CTA-group scheduler of the staged kernel: {next group, CTAs done, -, -}
   float2* pos;
   int4* meta;
   int16_t* wait;
@@ -67,6 +81,11 @@ struct DevParams {
 
 __device__ __forceinline__ uint32_t ld_grid(const uint32_t* p) { return __ldcg(p); }
 __device__ __forceinline__ void st_grid(uint32_t* p, uint32_t v) { __stcg(p, v); }
+__device__ __forceinline__ uint32_t smem_atomic_and(uint32_t addr_s, uint32_t v) {   // ATOMS.AND with the old value
+  uint32_t old;
+  asm volatile("atom.shared.and.b32 %0, [%1], %2;" : "=r"(old) : "r"(addr_s), "r"(v) : "memory");
+  return old;
+}
 
 // ---- sm_90+/sm_100a async-copy (TMA bulk) and mbarrier wrappers -----------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
@@ -144,12 +163,28 @@ __device__ __forceinline__ void bulk_g2s_s_hint(uint32_t dst_s, const void* src_
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 
-__device__ __forceinline__ float code_to_f32(uint32_t code, float u) {
-  // 0 -> 0, 1 -> 1, 2 -> U, 3 -> pad (-1)
-  return (code & 2u) ? ((code & 1u) ? -1.0f : u) : (float)(code & 1u);
+// ---- cell codes ---------------------------------------------------------------------------------------------------
+// Everything that turns state into values goes through a 2-bit CODE: 0 mapped (value 0), 1 normal (value 1),
+// 2 pad (window cell outside the grid: -1 / 255), 3 anomalous (value U).  code = unmapped | (anomalous_or_pad << 1).
+constexpr uint32_t CODE_MAPPED = 0u, CODE_NORMAL = 1u, CODE_PAD = 2u, CODE_ANOM = 3u;
+
+// Is `cell` (flat index) / (x, y) one of the env's anomalous cells?
+__device__ __forceinline__ bool is_anomalous(const DevParams& p, int env, int cell, int x, int y) {
+  if (p.list_mode) {
+    const uint16_t* l = p.alist + (size_t)env * 8;
+    const uint32_t key = (uint32_t)x | ((uint32_t)y << 8);
+    bool hit = false;
+    for (int k = 0; k < p.n_anom; ++k) hit = hit || (l[k] == key);
+    return hit;
+  }
+  return (__ldcg(p.anomp + (size_t)env * p.env_words + (cell >> 5)) >> (cell & 31)) & 1u;
 }
-__device__ __forceinline__ uint32_t code_to_u8(uint32_t code, uint32_t u) {
-  return (code & 2u) ? ((code & 1u) ? 255u : u) : (code & 1u);
+// Code of a cell of an env, read from HBM / L2 (state kernels, CTA kernel fallbacks; not the hot path).
+__device__ __forceinline__ uint32_t cell_code_global(const DevParams& p, int env, int cell) {
+  const uint32_t bit = (__ldcg(p.cov + (size_t)env * p.env_words + (cell >> 5)) >> (cell & 31)) & 1u;
+  if (!bit) return CODE_MAPPED;
+  const int y = cell / p.R, x = cell - y * p.R;
+  return is_anomalous(p, env, cell, x, y) ? CODE_ANOM : CODE_NORMAL;
 }
 
 // ---- Philox4x32-10 (Salmon et al., SC'11); same constants/round structure as oracle_philox4x32_10 ----

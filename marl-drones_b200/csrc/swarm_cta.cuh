@@ -1,9 +1,12 @@
-// swarm_cta.cuh — the fused env step for shapes the shared-memory-staged kernel does not take: more than 32 drones per
-// env, or a packed grid too large to stage per warp (the 256x256 stress config).  One CTA per env:
-//   one TMA bulk copy brings the env's packed grid (16 KiB at 256x256) into the CTA's shared memory,
-//   warp 0 runs stages (1)-(3) in index-ordered chunks of 32 drones (clears go to shared memory and, write-through, to HBM),
-//   then the WHOLE CTA streams stage (4) from shared memory with 128-bit stores (a 256x256 float obs is 256 KiB per env:
-//   the emission is the kernel).  Grids beyond the shared-memory budget fall back to the HBM-resident grid.
+// swarm_cta.cuh — the fused env step for shapes the shared-memory-staged warp kernel does not take: more than 32 drones per
+// env, a coverage map too large to stage per warp (the 256x256 stress config), or PLANE-mode anomalies (more than 8
+// anomalous cells, or a side longer than 256).  One CTA per env:
+//   TMA bulk copies bring the env's coverage plane (8 KiB at 256x256; plus the anomaly plane in PLANE mode, or the 16-byte
+//   list) into the CTA's shared memory,
+//   stages (1)-(2) run on all threads, one drone per thread (production path), or on warp 0 in index-ordered chunks of 32
+//   drones (generic path); cleared bits go to shared memory and, write-through, to HBM,
+//   warp 0 runs stage (3), then the WHOLE CTA streams stage (4) from shared memory (a 256x256 float obs is 256 KiB per env:
+//   the emission is the kernel).  Planes beyond the shared-memory budget fall back to the HBM-resident state.
 // Reference lines per stage: see swarm_step.cuh.
 #pragma once
 #include "swarm_common.cuh"
@@ -12,17 +15,35 @@
 
 namespace swarm {
 
+// The env's state as the CTA sees it: planes / list in shared memory when staged, else null (HBM accessors are used).
+struct CtaView {
+  uint32_t* sc;          // coverage plane (shared) or null
+  const uint32_t* sa;    // anomaly plane (shared, PLANE mode) or null
+  const uint16_t* sl;    // anomaly list (shared, LIST mode) or null
+};
+
+__device__ __forceinline__ bool cta_is_anomalous(const DevParams& p, const CtaView& v, int env, int cell, int x, int y) {
+  if (v.sl) {
+    const uint32_t key = (uint32_t)x | ((uint32_t)y << 8);
+    bool hit = false;
+    for (int k = 0; k < p.n_anom; ++k) hit = hit || (v.sl[k] == key);
+    return hit;
+  }
+  if (v.sa) return (v.sa[cell >> 5] >> (cell & 31)) & 1u;
+  return is_anomalous(p, env, cell, x, y);
+}
+
 // Stages (1)-(3) (+ auto-reset) of one env by one warp.
-// `sg`: the env's packed grid in shared memory (null = work on the HBM copy only).
-// `pre_pk` (may be null): stages (1)-(2) were already run by the whole CTA (move_scatter_cta); *pre_pk holds the env's packed
-// coverage totals (reward | cells << 16 | anomalous << 24) and this warp runs stage (3) only.
-__device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc, uint32_t* sg,
+// `pre_pk` (may be null): stages (1)-(2) were already run by the whole CTA (move_drone / scatter_drone); *pre_pk holds the
+// env's packed coverage totals (reward | cells << 16 | anomalous << 24) and this warp runs stage (3) only.
+// Returns true when the env was reset (the caller refreshes its shared-memory view).
+__device__ __forceinline__ bool step_env_warp(const DevParams& p, const StepIO& io, int t, int env, int lane, StatAcc& acc, const CtaView& v,
                                               const int* pre_pk = nullptr, float2* sp = nullptr, const int4* m_pre = nullptr) {
   constexpr int TS = 32;
   const int flags = pre_pk ? (io.flags & ~(F_MOVE | F_SCATTER)) : io.flags;
   const int D = p.D;
   const int nch = (D + TS - 1) / TS;
-  uint32_t* g = p.grid + (size_t)env * p.env_words;
+  uint32_t* g = p.cov + (size_t)env * p.env_words;
   int rew = 0, ncl = 0, nan = 0;
   float x = 0.f, y = 0.f;   // chunk-0 drone of this lane (all drones when D <= 32)
 
@@ -53,9 +74,9 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
     if (c == 0) { x = q.x; y = q.y; }
     if ((flags & F_SCATTER) && p.cd_fast) {   // stage (2), cd <= 0.5: the only candidate is the nearest lattice cell
       bool cand = false;
-      int cell = 0;
+      int cell = 0, cx = 0, cy = 0;
       if (active) {
-        const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
+        cx = (int)floorf(q.x + 0.5f); cy = (int)floorf(q.y + 0.5f);
         const double dx = (double)cx - (double)q.x, dy = (double)cy - (double)q.y;
         cand = dx * dx + dy * dy < p.cd2_thr;
         cell = cy * p.R + cx;
@@ -64,10 +85,9 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
       const unsigned m = __match_any_sync(FULL, key);
       if (cand && lane == __ffs(m) - 1) {
         const int k = __popc(m);
-        uint32_t* wp = g + (cell >> 4);
-        const int sh = (cell & 15) * 2;
-        const uint32_t code = ((sg ? sg[cell >> 4] : ld_grid(wp)) >> sh) & 3u;
-        if (code) {
+        uint32_t* wp = g + (cell >> 5);
+        const uint32_t bit = 1u << (cell & 31);
+        if ((v.sc ? v.sc[cell >> 5] : ld_grid(wp)) & bit) {
           bool clear = true;
           if (p.has_wait) {   // dwell (App. B.2)
             int16_t* w = p.wait + (size_t)env * p.RC + cell;
@@ -76,11 +96,12 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
             else if (wv > 0) *w = 0;
           }
           if (clear) {
-            atomicAnd(wp, ~(3u << sh));
-            if (sg) atomicAnd(sg + (cell >> 4), ~(3u << sh));
-            rew += 10 + (code == 2u ? 20 : 0);   // 10 + _check_uncertain_mapped (noVis_sim.py:83-84,104-110)
+            atomicAnd(wp, ~bit);
+            if (v.sc) atomicAnd(v.sc + (cell >> 5), ~bit);
+            const int an = cta_is_anomalous(p, v, env, cell, cx, cy) ? 1 : 0;
+            rew += 10 + 20 * an;   // 10 + _check_uncertain_mapped (noVis_sim.py:83-84,104-110)
             ncl += 1;
-            nan += (code == 2u);
+            nan += an;
           }
         }
       }
@@ -89,7 +110,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
   }
   if ((flags & F_SCATTER) && !p.cd_fast) {
     __syncwarp();
-    if (lane == 0) scatter_sequential(p, env, g, sg, rew, ncl, nan);
+    if (lane == 0) scatter_sequential(p, env, v.sc, rew, ncl, nan);
   }
 #pragma unroll
   for (int o = 16; o > 0 && !pre_pk; o >>= 1) {
@@ -98,6 +119,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
     nan += __shfl_xor_sync(FULL, nan, o);
   }
 
+  bool did_reset = false;
   if (flags & F_REWARD) {   // stage (3)
     int4 m = make_int4(0, 0, 0, 0);
     if (lane == 0) m = m_pre ? *m_pre : __ldcg(p.meta + env);
@@ -127,10 +149,7 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
     const int episode = __shfl_sync(FULL, m.w, 0);
     if (do_reset) {
       reset_tile<TS>(p, env, episode + 1, lane, true);
-      if (sg)   // refresh the shared-memory copy from the freshly written HBM grid
-        for (int w = lane; w < p.env_words; w += 32) sg[w] = ld_grid(g + w);
-      if (sp)   // ... and the shared-memory positions from the reset ones
-        for (int d = lane; d < D; d += 32) sp[d] = __ldcg(p.pos + (size_t)env * D + d);
+      did_reset = true;
     }
   } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
     if (lane == 0) {
@@ -139,13 +158,14 @@ __device__ __forceinline__ void step_env_warp(const DevParams& p, const StepIO& 
     }
   }
   __syncwarp();
+  return did_reset;
 }
 
 // Stages (1)-(2) by the WHOLE CTA for collision_dist <= 0.5 without dwell (the production path): one thread per drone moves,
-// clips and tests its nearest lattice cell on the shared-memory grid.  Several drones on one cell: the return value of the
-// shared-memory atomicAnd elects exactly one of them (the one that still saw the code), so the cell is cleared and rewarded
-// once — the per-env reward is a sum, the order does not matter.  Totals are packed into *s_pk (<= 255 drones
-// can clear a cell per step: D <= 1024 drones, but at most 255 fit the 8-bit fields — larger D fall back to the warp path).
+// clips and tests its nearest lattice cell on the shared-memory plane.  Several drones on one cell: the return value of the
+// shared-memory atomicAnd elects exactly one of them (the one that still saw the bit), so the cell is cleared and rewarded
+// once — the per-env reward is a sum, the order does not matter.  Totals are packed into *s_pk (at most 255
+// drones fit the 8-bit fields — larger D fall back to the warp path).
 __device__ __forceinline__ float2 move_drone(const DevParams& p, const StepIO& io, int t, int env, int d) {   // stage (1)
   float2* pp = p.pos + (size_t)env * p.D + d;
   float2 q = __ldcg(pp);
@@ -160,37 +180,36 @@ __device__ __forceinline__ float2 move_drone(const DevParams& p, const StepIO& i
   __stcg(pp, q);
   return q;
 }
-__device__ __forceinline__ void scatter_drone(const DevParams& p, int env, float2 q, uint32_t* sg, int* s_pk) {   // stage (2)
+__device__ __forceinline__ void scatter_drone(const DevParams& p, const CtaView& v, int env, float2 q, int* s_pk) {   // stage (2)
   const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
   const double dx = (double)cx - (double)q.x, dy = (double)cy - (double)q.y;
   if (dx * dx + dy * dy < p.cd2_thr) {          // sqrt(d2) < collision_dist (noVis_sim.py:81)
-    const int cell = cy * p.R + cx, sh = (cell & 15) * 2;
-    if ((sg[cell >> 4] >> sh) & 3u) {
-      const uint32_t code = (atomicAnd(sg + (cell >> 4), ~(3u << sh)) >> sh) & 3u;
-      if (code) {
-        atomicAnd(p.grid + (size_t)env * p.env_words + (cell >> 4), ~(3u << sh));   // write-through to HBM
-        atomicAdd(s_pk, (10 + (code == 2u ? 20 : 0)) | (1 << 16) | ((code == 2u ? 1 : 0) << 24));
+    const int cell = cy * p.R + cx;
+    const uint32_t bit = 1u << (cell & 31);
+    if (v.sc[cell >> 5] & bit) {
+      if (atomicAnd(v.sc + (cell >> 5), ~bit) & bit) {
+        atomicAnd(p.cov + (size_t)env * p.env_words + (cell >> 5), ~bit);   // write-through to HBM
+        const int an = cta_is_anomalous(p, v, env, cell, cx, cy) ? 1 : 0;
+        atomicAdd(s_pk, (10 + 20 * an) | (1 << 16) | (an << 24));
       }
     }
   }
 }
 
-// CTA-wide stage (4) from the shared-memory grid.
+// CTA-wide stage (4) from the shared-memory view.  FULL: bits -> elements with 128-bit stores (+ the LIST patch after a
+// CTA barrier); WINDOW: one item = one window row of one drone.
 template <typename OT>
-__device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint32_t* sg, int env, int tid, int nthr, OT* __restrict__ obs,
+__device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const CtaView& v, int env, int tid, int nthr, OT* __restrict__ obs,
                                                   const float2* sp = nullptr) {
   const ObsCvt<OT> cvt(p);
   if (p.obs_mode == 0) {
-    const int RC = p.RC;
-    OT* o = obs + (size_t)env * RC;
-    if ((RC & 3) == 0 && ((uintptr_t)o & 15) == 0) {
-      const int nq = RC >> 2;
-#pragma unroll 4
-      for (int q = tid; q < nq; q += nthr) cvt.store4(o + 4 * q, (sg[q >> 2] >> ((q & 3) * 8)) & 0xffu);
-    } else {
-      for (int c = tid; c < RC; c += nthr) o[c] = cvt.one((sg[c >> 4] >> ((c & 15) * 2)) & 3u);
+    OT* o = obs + (size_t)env * p.RC;
+    emit_full_bits<OT>(p, cvt, v.sc, v.sa, 1, tid, nthr, o);
+    if (v.sl) {
+      __syncthreads();   // the patch overwrites cells other threads have just written
+      emit_full_patch<OT>(p, cvt, v.sc, v.sl, 1, tid, nthr, o);
     }
-  } else {   // one item = one window row of one drone
+  } else {
     const int W = p.W, WW = W * W, h = (W - 1) >> 1, nitem = p.D * W;
     const float2* ps = p.pos + (size_t)env * p.D;
     OT* o = obs + (size_t)env * p.D * WW;
@@ -202,10 +221,11 @@ __device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint
       const bool row_ok = (unsigned)gy < (unsigned)p.C;
       for (int a = 0; a < W; ++a) {
         const int gx = cx - h + a;
-        uint32_t code = 3u;
+        uint32_t code = CODE_PAD;
         if (row_ok && (unsigned)gx < (unsigned)p.R) {
           const int cell = gy * p.R + gx;
-          code = (sg[cell >> 4] >> ((cell & 15) * 2)) & 3u;
+          code = (v.sc[cell >> 5] >> (cell & 31)) & 1u;
+          if (code && cta_is_anomalous(p, v, env, cell, gx, gy)) code = CODE_ANOM;
         }
         dst[a] = cvt.one(code);
       }
@@ -213,14 +233,18 @@ __device__ __forceinline__ void emit_obs_cta_smem(const DevParams& p, const uint
   }
 }
 
-// `staged` != 0: dynamic shared memory holds env_words words (+ slack) and the grid is staged through it.
+// `staged` != 0: dynamic shared memory holds the env's plane(s) (+ slack) and the state is staged through it.
 template <typename OT>
 __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io, int staged) {
   extern __shared__ __align__(128) unsigned char cta_smem[];
   __shared__ uint64_t bar;
-  __shared__ int s_pk;
+  __shared__ int s_pk, s_reset;
+  __shared__ __align__(16) uint16_t s_list[8];
   __shared__ float2 s_pos[256];   // this step's positions of the env (wide path): spread test and window emission read them here
-  uint32_t* const sg = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
+  CtaView v;
+  v.sc = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
+  v.sa = (staged && !p.list_mode) ? reinterpret_cast<const uint32_t*>(cta_smem) + p.env_words : nullptr;
+  v.sl = (staged && p.list_mode) ? s_list : nullptr;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int flags = io.flags;
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
@@ -234,18 +258,25 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   __syncthreads();
   uint32_t phase = 0;
   StatAcc acc;
+  const uint32_t plane_bytes = (uint32_t)p.env_words * 4u;
+  auto load_view = [&](int env) {   // one thread: the env's plane(s) / list by TMA
+    mbar_expect_tx(&bar, p.list_mode ? plane_bytes + 16u : 2u * plane_bytes);
+    bulk_g2s(v.sc, p.cov + (size_t)env * p.env_words, plane_bytes, &bar);
+    if (p.list_mode) bulk_g2s(s_list, p.alist + (size_t)env * 8, 16u, &bar);
+    else bulk_g2s(const_cast<uint32_t*>(v.sa), p.anomp + (size_t)env * p.env_words, plane_bytes, &bar);
+  };
   // production path: stages (1)-(2) on all threads, one drone per thread (30 * 255 < 2^16 keeps the packed totals exact)
   const bool wide = staged && (flags & (F_MOVE | F_SCATTER | F_REWARD)) == (F_MOVE | F_SCATTER | F_REWARD) && p.cd_fast && !p.has_wait &&
                     p.D <= 255 && p.D < (int)blockDim.x;
   for (int env = blockIdx.x; env < p.N; env += gridDim.x) {
     int4 m_pre = make_int4(0, 0, 0, 0);
-    if (staged && threadIdx.x == 0) {   // one TMA bulk copy: the env's whole packed grid
-      mbar_expect_tx(&bar, (uint32_t)p.env_words * 4u);
-      bulk_g2s(sg, p.grid + (size_t)env * p.env_words, (uint32_t)p.env_words * 4u, &bar);
-      if (wide) m_pre = __ldcg(p.meta + env);   // in flight together with the grid and the positions
+    if (staged && threadIdx.x == 0) {
+      load_view(env);
+      if (wide) m_pre = __ldcg(p.meta + env);   // in flight together with the planes and the positions
     }
     bool landed = !staged;
     for (int t = 0; t < io.T; ++t) {
+      if (threadIdx.x == 0) s_reset = 0;
       if (stepping && wide) {
         // stage (1) needs no grid: its loads overlap the bulk copy
         const bool mine = (int)threadIdx.x < p.D;
@@ -256,39 +287,48 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
           s_pos[threadIdx.x] = q;
         }
         if (!landed) { mbar_wait(&bar, phase); phase ^= 1u; landed = true; }
-        __syncthreads();   // s_pk is zero, the grid has landed
-        if (mine) scatter_drone(p, env, q, sg, &s_pk);
+        __syncthreads();   // s_pk is zero, the planes have landed
+        if (mine) scatter_drone(p, v, env, q, &s_pk);
         __syncthreads();   // clears (shared memory), positions (s_pos) and totals are visible to warp 0
-        if (warp == 0) step_env_warp(p, io, t, env, lane, acc, sg, &s_pk, s_pos, t == 0 ? &m_pre : nullptr);
-        __syncthreads();   // warp 0's grid / position updates (auto-reset) are visible to the CTA
+        if (warp == 0 && step_env_warp(p, io, t, env, lane, acc, v, &s_pk, s_pos, t == 0 ? &m_pre : nullptr) && lane == 0) s_reset = 1;
+        __syncthreads();   // warp 0's updates (auto-reset) are visible to the CTA
       } else {
         if (!landed) { mbar_wait(&bar, phase); phase ^= 1u; landed = true; }
+        __syncthreads();
         if (stepping) {
-          if (warp == 0) step_env_warp(p, io, t, env, lane, acc, sg);
-          __syncthreads();   // warp 0's grid / position updates are visible to the CTA
+          if (warp == 0 && step_env_warp(p, io, t, env, lane, acc, v) && lane == 0) s_reset = 1;
+          __syncthreads();   // warp 0's updates are visible to the CTA
         }
+      }
+      if (staged && s_reset) {   // rare: the env was reset in HBM — bring the fresh planes / list / positions on chip
+        fence_proxy_async();
+        __syncthreads();
+        if (threadIdx.x == 0) load_view(env);
+        if (stepping && wide && (int)threadIdx.x < p.D) s_pos[threadIdx.x] = __ldcg(p.pos + (size_t)env * p.D + threadIdx.x);
+        mbar_wait(&bar, phase); phase ^= 1u;
+        __syncthreads();
       }
       if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
         OT* o = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * p.N * p.obs_per_env);
-        if (staged) emit_obs_cta_smem<OT>(p, sg, env, threadIdx.x, blockDim.x, o, (stepping && wide) ? s_pos : nullptr);
+        if (staged) emit_obs_cta_smem<OT>(p, v, env, threadIdx.x, blockDim.x, o, (stepping && wide) ? s_pos : nullptr);
         else emit_obs_global<OT>(p, env, threadIdx.x, blockDim.x, o);
-        if (stepping && t + 1 < io.T) __syncthreads();   // emission reads precede the next step's clears
       }
+      if (t + 1 < io.T) __syncthreads();   // emission reads precede the next step's clears; s_reset is re-armed
     }
     if (staged) {
-      fence_proxy_async();   // generic accesses to the staged grid precede the next env's bulk copy
+      fence_proxy_async();   // generic accesses to the staged view precede the next env's bulk copies
       __syncthreads();
     }
   }
 
   if (io.stats && (flags & F_REWARD)) {   // only warp 0 accumulated
     if (warp == 0) {
-      long long v[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
+      long long vv[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(FULL, v[k], o);
-        if (lane == 0 && v[k] != 0) atomicAdd(io.stats + 2 + k, (unsigned long long)v[k]);
+        for (int o = 16; o > 0; o >>= 1) vv[k] += __shfl_xor_sync(FULL, vv[k], o);
+        if (lane == 0 && vv[k] != 0) atomicAdd(io.stats + 2 + k, (unsigned long long)vv[k]);
       }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {

@@ -24,7 +24,11 @@ __global__ void __launch_bounds__(256) reset_kernel(const __grid_constant__ DevP
   }
 }
 
-// set_state: boundary int8 [count][RC] (values 0 / 1 / U, obs order) -> packed grid; recomputes `remaining`.
+// set_state: boundary int8 [count][RC] (values 0 / 1 / U, obs order) -> coverage plane + anomalies; recomputes `remaining`.
+// LIST mode: the cells of value U become the env's list (at most n_anamolous of them — more is flagged in the device error
+// word, SWARM_DEVERR_BAD_STATE); when the injected grid holds fewer (a state from the middle of an episode: found anomalies
+// read 0), the spare entries repeat a listed cell, or name a mapped cell / an out-of-grid key when there is none — entries
+// that can never turn a normal cell into an anomalous one.
 __global__ void __launch_bounds__(256) set_state_kernel(const __grid_constant__ DevParams p, const int8_t* grid, const float* pos,
                                                         const int* t, const int16_t* wait, int first, int count) {
   const int lane = threadIdx.x & 31;
@@ -36,20 +40,40 @@ __global__ void __launch_bounds__(256) set_state_kernel(const __grid_constant__ 
     if (grid) {
       const int8_t* src = grid + (size_t)e * p.RC;
       for (int w = lane; w < p.env_words; w += 32) {
-        uint32_t word = 0;
-        for (int k = 0; k < 16; ++k) {
-          const int c = w * 16 + k;
+        uint32_t cw = 0u, aw = 0u;
+        for (int k = 0; k < 32; ++k) {
+          const int c = w * 32 + k;
           if (c < p.RC) {
             const int v = src[c];
-            const uint32_t code = v <= 0 ? 0u : (v == p.U ? 2u : 1u);
-            word |= code << (2 * k);
-            rem += code != 0u;
+            if (v > 0) { cw |= 1u << k; ++rem; }
+            if (v == p.U) aw |= 1u << k;
           }
         }
-        st_grid(p.grid + (size_t)env * p.env_words + w, word);
+        st_grid(p.cov + (size_t)env * p.env_words + w, cw);
+        if (p.anomp) st_grid(p.anomp + (size_t)env * p.env_words + w, aw);
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) rem += __shfl_xor_sync(FULL, rem, o);
+      if (p.alist) {   // one lane walks the grid in flat order (state injection is not a hot path)
+        __syncwarp();
+        if (lane == 0) {
+          uint16_t* l = p.alist + (size_t)env * 8;
+          int n = 0, mapped = -1;
+          for (int c = 0; c < p.RC; ++c) {
+            const int v = src[c];
+            if (v == p.U) {
+              if (n < p.n_anom) l[n] = (uint16_t)((c % p.R) | ((c / p.R) << 8));
+              ++n;
+            } else if (v <= 0 && mapped < 0) mapped = c;
+          }
+          if (n > p.n_anom) atomicOr(p.err, 8);
+          uint16_t fill = 0xffffu;                                   // (255, 255): outside every grid but 256 x 256
+          if (n > 0) fill = l[0];
+          else if (mapped >= 0) fill = (uint16_t)((mapped % p.R) | ((mapped / p.R) << 8));
+          else if (p.R == 256 && p.C == 256 && p.n_anom > 0) atomicOr(p.err, 8);
+          for (int k = min(n, p.n_anom); k < 8; ++k) l[k] = fill;
+        }
+      }
     }
     if (pos)
       for (int k = lane; k < p.D; k += 32)
@@ -75,8 +99,8 @@ __global__ void __launch_bounds__(256) get_state_kernel(const __grid_constant__ 
     const int env = first + e;
     if (grid)
       for (int c = lane; c < p.RC; c += 32) {
-        const uint32_t code = (ld_grid(p.grid + (size_t)env * p.env_words + (c >> 4)) >> ((c & 15) * 2)) & 3u;
-        grid[(size_t)e * p.RC + c] = (int8_t)(code == 2u ? p.U : (int)code);
+        const uint32_t code = cell_code_global(p, env, c);
+        grid[(size_t)e * p.RC + c] = (int8_t)(code == CODE_ANOM ? p.U : (int)code);
       }
     if (pos)
       for (int k = lane; k < p.D; k += 32) {
@@ -118,7 +142,7 @@ __global__ void __launch_bounds__(256) greedy_kernel(const __grid_constant__ Dev
   const long long n = (long long)p.N * p.D;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const int env = (int)(i / p.D);
-    const uint32_t* g = p.grid + (size_t)env * p.env_words;
+    const uint32_t* g = p.cov + (size_t)env * p.env_words;
     const float2 q = p.pos[i];
     const double x = q.x, y = q.y;
     double best = 0.0;
@@ -127,7 +151,7 @@ __global__ void __launch_bounds__(256) greedy_kernel(const __grid_constant__ Dev
     for (int gx = 0; gx < p.R; ++gx)
       for (int gy = 0; gy < p.C; ++gy) {
         const int cell = gy * p.R + gx;
-        if ((ld_grid(g + (cell >> 4)) >> ((cell & 15) * 2)) & 3u) {
+        if ((ld_grid(g + (cell >> 5)) >> (cell & 31)) & 1u) {
           const double d2 = (gx - x) * (gx - x) + (gy - y) * (gy - y);
           if (!have || best == 0.0 || d2 < best) { have = true; best = d2; bx = gx; by = gy; }
         }
