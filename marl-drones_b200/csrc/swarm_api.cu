@@ -90,7 +90,7 @@ static int align16(long long v) { return (int)((v + 15) / 16 * 16); }
 static void warp_bytes(const SwarmConfig* c, const DevParams* p, int ts, int* stage, int* in_w) {
   const int epw = 32 / ts;
   *stage = stage_bytes_for(c, epw);
-  *in_w = epw * (p->env_words * 4 + 16 + 16) + align16((long long)epw * c->n_drones * 8) + align16((long long)epw * c->n_drones);
+  *in_w = epw * (p->env_words * 4 + 32 + 16) + align16((long long)epw * c->n_drones * 8) + align16((long long)epw * c->n_drones);
 }
 
 // Smallest power-of-two tile >= D (min 4), widened while the batch would give too few warps to fill the GPU.
@@ -215,30 +215,51 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   e->staged = e->ts != 0;
   if (!e->staged) e->ts = 32;
   if (e->staged) {
-    // CTA shape and ring depth: the (warps per CTA, stages) pair that keeps most warps resident in an SM's 227 KB (register
-    // cap: SWARM_MINB CTAs of 8 warps), then the deepest ring, then the larger CTA.  SWARM_WPB / SWARM_STAGES override.
+    // CTA shape and ring depth: the (warps per CTA w, stages S) pair with the cheapest schedule.  Model: an SM keeps `ctas`
+    // CTAs resident (shared memory: 227 KB; registers: 72 per thread under the kernel's launch bounds); the
+    // ncg = ceil(N / (w * EPW)) CTA-groups are dealt round-robin over SMs x ctas slots, so an SM works through
+    // rounds = ceil(ceil(ncg / SMs) / ctas) rounds of min(ctas, ceil(ncg / SMs)) * w warps each, a round costing a latency
+    // floor plus the warps it holds.  Ties: deeper ring, then more busy SMs, then the larger CTA.
+    // cfg3 (65 536 envs x 16 drones): w = 14, S = 3, 2 CTAs per SM -> 2341 CTA-groups over 296 slots = 8 rounds at 98.8 %
+    // (round 1's fixed 8-warp CTAs: 4096 over 444 = 9.22 -> 10 rounds); 8192 envs (cfg3 sharded over 8 GPUs) and cfg4 become
+    // ONE round.  SWARM_WPB / SWARM_STAGES override.
     int stage = 0, in_w = 0;
     warp_bytes(c, &p, e->ts, &stage, &in_w);
     p.stage_bytes = stage;
+    const int epw = 32 / e->ts;
     int smax = 4, wforce = 0;
-    if (const char* v = getenv("SWARM_STAGES")) { const int x = atoi(v); if (x >= 2 && x <= 6) smax = x; }
-    if (const char* v = getenv("SWARM_WPB")) { const int x = atoi(v); if (x == 2 || x == 4 || x == 8) wforce = x; }
+    if (const char* v = getenv("SWARM_STAGES")) { const int x = atoi(v); if (x >= 2 && x <= MAX_STAGES) smax = x; }
+    if (const char* v = getenv("SWARM_WPB")) { const int x = atoi(v); if (x >= 1 && x <= SWARM_MAXT / 32) wforce = x; }
     const long long stat = 7 * 1024 + 1024;   // static shared memory of the kernel (LUT, pad tables, barriers) + the driver's 1 KB
-    int best_warps = -1, best_s = 0;
+    const int kRegs = 72;
+    double best_cost = 1e30;
+    int best_s = 0, best_busy = 0;
     e->wpb = 8;
-    for (int w = 8; w >= 2; w >>= 1) {
+    for (int w = SWARM_MAXT / 32; w >= 1; --w) {
       if (wforce && w != wforce) continue;
       for (int S = smax; S >= 2; --S) {
         const long long smem = (long long)w * stage + (long long)S * w * in_w + 64 + stat;
         if (smem > 227 * 1024) continue;
-        long long warps = (227 * 1024) / smem * w;
-        if (warps > 24) warps = 24;
-        if (warps > best_warps || (warps == best_warps && S > best_s)) { best_warps = (int)warps; best_s = S; e->wpb = w; }
+        long long ctas = (227 * 1024) / smem;
+        const long long by_regs = 65536 / ((long long)w * 32 * kRegs), by_warps = 64 / w;
+        if (ctas > by_regs) ctas = by_regs;
+        if (ctas > by_warps) ctas = by_warps;
+        if (ctas > 32) ctas = 32;
+        if (ctas < 1) continue;
+        const long long ncg = ((long long)p.N + (long long)w * epw - 1) / ((long long)w * epw);
+        const long long per_sm = (ncg + sms - 1) / sms;
+        const long long rounds = (per_sm + ctas - 1) / ctas;
+        const long long act = per_sm < ctas ? per_sm : ctas;
+        const double cost = (double)rounds * (8.0 + (double)(act * w));
+        const int busy = (int)(ncg < sms ? ncg : sms);
+        if (cost < best_cost - 1e-9 || (cost < best_cost + 1e-9 && (S > best_s || (S == best_s && busy > best_busy)))) {
+          best_cost = cost; best_s = S; best_busy = busy; e->wpb = w;
+        }
       }
     }
     p.n_stages = best_s > 0 ? best_s : 2;
-    const long long epc = (long long)e->wpb * (32 / e->ts);
-    const int covb = (int)(epc * p.env_words * 4), listb = (int)(epc * 16), posb = align16(epc * c->n_drones * 8), metab = (int)(epc * 16);
+    const long long epc = (long long)e->wpb * epw;
+    const int covb = (int)(epc * p.env_words * 4), listb = (int)(epc * 32), posb = align16(epc * c->n_drones * 8), metab = (int)(epc * 16);
     const int actb = align16(epc * c->n_drones);
     p.off_alist = covb;
     p.off_pos = covb + listb;
@@ -260,7 +281,7 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   cudaError_t err = cudaSuccess;
   auto alloc = [&](void** ptr, size_t bytes) { if (err == cudaSuccess) err = cudaMalloc(ptr, bytes ? bytes : 16); };
   alloc((void**)&p.cov, N * p.env_words * sizeof(uint32_t));
-  if (p.list_mode) alloc((void**)&p.alist, N * 8 * sizeof(uint16_t));
+  if (p.list_mode) alloc((void**)&p.alist, N * 8 * sizeof(uint32_t));
   else alloc((void**)&p.anomp, N * p.env_words * sizeof(uint32_t));
   alloc((void**)&p.sched, 16);
   alloc((void**)&p.pos, N * p.D * sizeof(float2));
@@ -372,8 +393,8 @@ static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st
   // FAST: every stage in one pass, uint8 actions, cd <= 0.5, no dwell — the swarm_step / swarm_rollout production path
   const bool fast = (io.flags & F_ALL) == F_ALL && io.act_dtype == SWARM_ACT_U8 && p.cd_fast && !p.has_wait && p.f32_exact;
   // LEAN: the FAST kernel with the tail / rollout / alignment bookkeeping folded away (see step_warp_kernel)
-  const int epc = e->wpb * (32 / TS);
-  const bool lean = fast && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epc == 0 &&
+  const int epw = 32 / TS;
+  const bool lean = fast && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epw == 0 && (epw * TS) % 16 == 0 &&
                     ((((uintptr_t)io.actions) | ((uintptr_t)io.obs_out)) & 15) == 0 && !getenv("SWARM_NO_LEAN");
   if (p.obs_mode == SWARM_OBS_FULL) {
     if (lean) return launch_warp_inst<TS, OT, 0, 0, true, true>(e, io, st, blocks, smem);

@@ -4,8 +4,8 @@
 //   cov   uint32 [N][env_words]   COVERAGE MAP, 1 bit per cell, 32 cells per word, flat cell index c = y*R + x (the
 //                                 reference's obs order, A2C/noVis_sim.py:168-170): bit = 1 <=> the cell is still unmapped
 //                                 (reference grid value > 0).  Bits past R*C are 0.  env_words is a multiple of 4 (16 B).
-//   alist uint16 [N][8]           LIST mode (n_anamolous <= 8 and R, C <= 256 — every reference call site): the env's
-//                                 anomalous cells as x | y << 8, entries >= n_anamolous unused.  Static within an episode:
+//   alist uint32 [N][8]           LIST mode (n_anamolous <= 8 and R, C <= 256 — every reference call site): the env's
+//                                 anomalous cells as x | y << 16, entries >= n_anamolous unused.  Static within an episode:
 //                                 a cell's value is  bit ? (listed ? U : 1) : 0, so "anomaly found" is the cleared bit.
 //   anomp uint32 [N][env_words]   PLANE mode (anything else): the anomalous cells as a second bit plane (static per episode).
 //   pos   float2 [N][D]           (x, y) = reference n_drones_pos[i]
@@ -45,7 +45,7 @@ struct DevParams {
   int cd_fast;        // collision_dist <= 0.5: at most one lattice cell can be hit
   int scan_m;         // ceil(cd) + 1: half-width of the bounded scan window for cd > 0.5
   int env_words;      // uint32 words per env of ONE bit plane (multiple of 4)
-  int list_mode;      // 1: anomalies in `alist` (x | y << 8, n_anom <= 8, R, C <= 256); 0: second bit plane `anomp`
+  int list_mode;      // 1: anomalies in `alist` (x | y << 16, n_anom <= 8, R, C <= 256); 0: second bit plane `anomp`
   int f32_exact;      // positions / squared distances are exact in float32 (step_size = m 2^-k, k <= 12, coordinates small):
                       // the FAST kernels compare in float; otherwise the generic double path runs
   float cd2_thr_f;    // smallest float >= cd2_thr:  d2 < cd2_thr <=> d2 < cd2_thr_f   for every d2 that is exactly a float
@@ -59,7 +59,7 @@ struct DevParams {
   double spread2_thr; // largest double z with sqrt(z) <= spread_thr: sqrt(d2) > thr <=> d2 > spread2_thr
   // warp-autonomous staged kernel (swarm_warp.cuh): per-warp shared-memory carve-up, bytes
   int stage_bytes;    // obs staging (WINDOW mode), multiple of 16, >= 16
-  int in_bytes;       // one CTA input stage for EPC = wpb*EPW envs: [cov EPC*env_words*4][alist EPC*16][pos EPC*D*8][meta EPC*16]
+  int in_bytes;       // one CTA input stage for EPC = wpb*EPW envs: [cov EPC*env_words*4][alist EPC*32][pos EPC*D*8][meta EPC*16]
                       // [actions EPC*D], each part 16 B aligned
   int off_alist, off_pos, off_meta, off_act;   // byte offsets inside an input stage
   int warp_smem;      // per-warp footprint used to size the CTA (stage_bytes + 2 * per-warp inputs + slack)
@@ -71,7 +71,7 @@ struct DevParams {
   PeerStats peers;
   uint32_t* cov;      // coverage bit plane
   uint32_t* anomp;    // anomaly bit plane (PLANE mode) or null
-  uint16_t* alist;    // anomaly list (LIST mode) or null
+  uint32_t* alist;    // anomaly list (LIST mode) or null
   int* sched;         // int[4] dynamic CTA-group scheduler of the staged kernel: {next group, CTAs done, -, -}
   float2* pos;
   int4* meta;
@@ -81,9 +81,10 @@ struct DevParams {
 
 __device__ __forceinline__ uint32_t ld_grid(const uint32_t* p) { return __ldcg(p); }
 __device__ __forceinline__ void st_grid(uint32_t* p, uint32_t v) { __stcg(p, v); }
-__device__ __forceinline__ uint32_t smem_atomic_and(uint32_t addr_s, uint32_t v) {   // ATOMS.AND with the old value
+// one thread's ATOMS.ADD (the C++ atomicAdd on shared memory comes with warp-aggregation code this use does not need)
+__device__ __forceinline__ uint32_t smem_atomic_inc(uint32_t addr_s) {
   uint32_t old;
-  asm volatile("atom.shared.and.b32 %0, [%1], %2;" : "=r"(old) : "r"(addr_s), "r"(v) : "memory");
+  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr_s) : "memory");
   return old;
 }
 
@@ -167,12 +168,15 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 // Everything that turns state into values goes through a 2-bit CODE: 0 mapped (value 0), 1 normal (value 1),
 // 2 pad (window cell outside the grid: -1 / 255), 3 anomalous (value U).  code = unmapped | (anomalous_or_pad << 1).
 constexpr uint32_t CODE_MAPPED = 0u, CODE_NORMAL = 1u, CODE_PAD = 2u, CODE_ANOM = 3u;
+// an anomaly-list entry that names no cell: (0x7000, 0x7000) is outside every LIST-mode grid (sides <= 256) and far enough
+// from the 16-bit limits for the packed window test of swarm_warp.cuh
+constexpr uint32_t LIST_EMPTY = 0x70007000u;
 
 // Is `cell` (flat index) / (x, y) one of the env's anomalous cells?
 __device__ __forceinline__ bool is_anomalous(const DevParams& p, int env, int cell, int x, int y) {
   if (p.list_mode) {
-    const uint16_t* l = p.alist + (size_t)env * 8;
-    const uint32_t key = (uint32_t)x | ((uint32_t)y << 8);
+    const uint32_t* l = p.alist + (size_t)env * 8;
+    const uint32_t key = (uint32_t)x | ((uint32_t)y << 16);
     bool hit = false;
     for (int k = 0; k < p.n_anom; ++k) hit = hit || (l[k] == key);
     return hit;

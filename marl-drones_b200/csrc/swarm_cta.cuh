@@ -1,7 +1,7 @@
 // swarm_cta.cuh — the fused env step for shapes the shared-memory-staged warp kernel does not take: more than 32 drones per
 // env, a coverage map too large to stage per warp (the 256x256 stress config), or PLANE-mode anomalies (more than 8
 // anomalous cells, or a side longer than 256).  One CTA per env:
-//   TMA bulk copies bring the env's coverage plane (8 KiB at 256x256; plus the anomaly plane in PLANE mode, or the 16-byte
+//   TMA bulk copies bring the env's coverage plane (8 KiB at 256x256; plus the anomaly plane in PLANE mode, or the 32-byte
 //   list) into the CTA's shared memory,
 //   stages (1)-(2) run on all threads, one drone per thread (production path), or on warp 0 in index-ordered chunks of 32
 //   drones (generic path); cleared bits go to shared memory and, write-through, to HBM,
@@ -19,12 +19,12 @@ namespace swarm {
 struct CtaView {
   uint32_t* sc;          // coverage plane (shared) or null
   const uint32_t* sa;    // anomaly plane (shared, PLANE mode) or null
-  const uint16_t* sl;    // anomaly list (shared, LIST mode) or null
+  const uint32_t* sl;    // anomaly list (shared, LIST mode) or null
 };
 
 __device__ __forceinline__ bool cta_is_anomalous(const DevParams& p, const CtaView& v, int env, int cell, int x, int y) {
   if (v.sl) {
-    const uint32_t key = (uint32_t)x | ((uint32_t)y << 8);
+    const uint32_t key = (uint32_t)x | ((uint32_t)y << 16);
     bool hit = false;
     for (int k = 0; k < p.n_anom; ++k) hit = hit || (v.sl[k] == key);
     return hit;
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   extern __shared__ __align__(128) unsigned char cta_smem[];
   __shared__ uint64_t bar;
   __shared__ int s_pk, s_reset;
-  __shared__ __align__(16) uint16_t s_list[8];
+  __shared__ __align__(16) uint32_t s_list[8];
   __shared__ float2 s_pos[256];   // this step's positions of the env (wide path): spread test and window emission read them here
   CtaView v;
   v.sc = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
@@ -260,9 +260,9 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   StatAcc acc;
   const uint32_t plane_bytes = (uint32_t)p.env_words * 4u;
   auto load_view = [&](int env) {   // one thread: the env's plane(s) / list by TMA
-    mbar_expect_tx(&bar, p.list_mode ? plane_bytes + 16u : 2u * plane_bytes);
+    mbar_expect_tx(&bar, p.list_mode ? plane_bytes + 32u : 2u * plane_bytes);
     bulk_g2s(v.sc, p.cov + (size_t)env * p.env_words, plane_bytes, &bar);
-    if (p.list_mode) bulk_g2s(s_list, p.alist + (size_t)env * 8, 16u, &bar);
+    if (p.list_mode) bulk_g2s(s_list, p.alist + (size_t)env * 8, 32u, &bar);
     else bulk_g2s(const_cast<uint32_t*>(v.sa), p.anomp + (size_t)env * p.env_words, plane_bytes, &bar);
   };
   // production path: stages (1)-(2) on all threads, one drone per thread (30 * 255 < 2^16 keeps the packed totals exact)

@@ -75,15 +75,15 @@ __device__ __forceinline__ void emit_full_bits(const DevParams& p, const ObsCvt<
       }
   }
 }
-// `sl`: the envs' anomaly lists (8 x uint16 per env) in shared or global memory
+// `sl`: the envs' anomaly lists (8 x uint32 per env) in shared or global memory
 template <typename OT>
-__device__ __forceinline__ void emit_full_patch(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* sc, const uint16_t* sl, int nenv, int tid,
+__device__ __forceinline__ void emit_full_patch(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* sc, const uint32_t* sl, int nenv, int tid,
                                                 int nthr, OT* __restrict__ o) {
   const int na = p.n_anom;
   for (int v = tid; v < nenv * na; v += nthr) {
     const int e = v / na, k = v - e * na;
     const uint32_t key = sl[e * 8 + k];
-    const int cell = (int)(key >> 8) * p.R + (int)(key & 0xffu);
+    const int cell = (int)(key >> 16) * p.R + (int)(key & 0xffffu);
     if ((sc[e * p.env_words + (cell >> 5)] >> (cell & 31)) & 1u) o[(size_t)e * p.RC + cell] = cvt.one(CODE_ANOM);
   }
 }

@@ -27,8 +27,8 @@ __global__ void __launch_bounds__(256) reset_kernel(const __grid_constant__ DevP
 // set_state: boundary int8 [count][RC] (values 0 / 1 / U, obs order) -> coverage plane + anomalies; recomputes `remaining`.
 // LIST mode: the cells of value U become the env's list (at most n_anamolous of them — more is flagged in the device error
 // word, SWARM_DEVERR_BAD_STATE); when the injected grid holds fewer (a state from the middle of an episode: found anomalies
-// read 0), the spare entries repeat a listed cell, or name a mapped cell / an out-of-grid key when there is none — entries
-// that can never turn a normal cell into an anomalous one.
+// read 0), the spare entries repeat a listed cell, or hold an out-of-grid key when there is none — entries that can never
+// turn a normal cell into an anomalous one.
 __global__ void __launch_bounds__(256) set_state_kernel(const __grid_constant__ DevParams p, const int8_t* grid, const float* pos,
                                                         const int* t, const int16_t* wait, int first, int count) {
   const int lane = threadIdx.x & 31;
@@ -57,20 +57,19 @@ __global__ void __launch_bounds__(256) set_state_kernel(const __grid_constant__ 
       if (p.alist) {   // one lane walks the grid in flat order (state injection is not a hot path)
         __syncwarp();
         if (lane == 0) {
-          uint16_t* l = p.alist + (size_t)env * 8;
+          uint32_t* l = p.alist + (size_t)env * 8;
           int n = 0, mapped = -1;
           for (int c = 0; c < p.RC; ++c) {
             const int v = src[c];
             if (v == p.U) {
-              if (n < p.n_anom) l[n] = (uint16_t)((c % p.R) | ((c / p.R) << 8));
+              if (n < p.n_anom) l[n] = (uint32_t)(c % p.R) | ((uint32_t)(c / p.R) << 16);
               ++n;
             } else if (v <= 0 && mapped < 0) mapped = c;
           }
           if (n > p.n_anom) atomicOr(p.err, 8);
-          uint16_t fill = 0xffffu;                                   // (255, 255): outside every grid but 256 x 256
+          uint32_t fill = LIST_EMPTY;                                // outside every LIST-mode grid
           if (n > 0) fill = l[0];
-          else if (mapped >= 0) fill = (uint16_t)((mapped % p.R) | ((mapped / p.R) << 8));
-          else if (p.R == 256 && p.C == 256 && p.n_anom > 0) atomicOr(p.err, 8);
+          else if (mapped >= 0) fill = (uint32_t)(mapped % p.R) | ((uint32_t)(mapped / p.R) << 16);
           for (int k = min(n, p.n_anom); k < 8; ++k) l[k] = fill;
         }
       }

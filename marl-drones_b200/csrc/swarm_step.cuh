@@ -49,7 +49,7 @@ __device__ __forceinline__ int load_action(const void* a, int dt, long long idx)
 // stage of the warp kernel (which then copies them out); generic addressing serves both.
 template <int TS>
 __device__ __forceinline__ void reset_planes(const DevParams& p, int env, int episode, int tl, bool doit, uint32_t* cov, uint32_t* anomp,
-                                             uint16_t* alist) {
+                                             uint32_t* alist) {
   int16_t* wt = p.has_wait ? p.wait + (size_t)(doit ? env : 0) * p.RC : nullptr;
   const long long gid = p.env_id_base + env;
   if (doit) {
@@ -58,7 +58,7 @@ __device__ __forceinline__ void reset_planes(const DevParams& p, int env, int ep
       cov[w] = n >= 32 ? 0xffffffffu : (n <= 0 ? 0u : ((1u << n) - 1u));
       if (anomp) anomp[w] = 0u;
     }
-    if (alist && tl < 8) alist[tl] = 0xffffu;
+    if (alist && tl < 8) alist[tl] = LIST_EMPTY;
     if (wt)
       for (int k = tl; k < p.RC; k += TS) wt[k] = (int16_t)p.dwell_normal;
   }
@@ -73,7 +73,7 @@ __device__ __forceinline__ void reset_planes(const DevParams& p, int env, int ep
       const int cell = (int)(b * (uint32_t)p.R + a);
       bool fresh = true;
       if (alist) {
-        const uint16_t key = (uint16_t)(a | (b << 8));
+        const uint32_t key = a | (b << 16);
         for (int k = 0; k < placed; ++k) fresh = fresh && alist[k] != key;
         if (fresh) alist[placed] = key;
       } else {

@@ -25,8 +25,15 @@
 #include "swarm_emit.cuh"
 #include "swarm_step.cuh"
 
+// Launch bounds of the staged kernel: CTAs of up to SWARM_MAXT threads, SWARM_MINB of them per SM — 2 x 448 threads = 28
+// resident warps at <= 72 registers.  The host picks the CTA shape (warps per CTA, ring depth) per env shape so that the
+// CTA-groups divide into whole rounds over the resident CTAs (swarm_api.cu, swarm_create): cfg3 = 14 warps x 2 CTAs per SM,
+// 2341 CTA-groups over 296 CTAs = 7.91 -> 8 rounds (round 1: 8 warps x 3 CTAs, 9.22 -> 10 rounds).
+#ifndef SWARM_MAXT
+#define SWARM_MAXT 448
+#endif
 #ifndef SWARM_MINB
-#define SWARM_MINB 3   // resident CTAs per SM the staged kernel is compiled for (register cap 65536 / (256 * SWARM_MINB))
+#define SWARM_MINB 2
 #endif
 
 namespace swarm {
@@ -34,18 +41,30 @@ namespace swarm {
 constexpr int MAX_STAGES = 6;
 
 // ---- window helpers (W == 5 fast path) --------------------------------------------------------------------------------
-// Anomalous cells of the env that fall inside the 5x5 window whose corner is (wx0, wy0): bit dy*5+dx.  `lv` = the env's list
-// (8 x uint16, x | y << 8) as loaded with one LDS.128; n is warp-uniform.
-__device__ __forceinline__ uint32_t window_anomalies5(const uint4 lv, int n, int wx0, int wy0) {
-  uint32_t A = 0u;
-  const uint32_t w[4] = {lv.x, lv.y, lv.z, lv.w};
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    if (k < n) {
-      const uint32_t e = (k & 1) ? (w[k >> 1] >> 16) : (w[k >> 1] & 0xffffu);
-      const int dx = (int)(e & 0xffu) - wx0, dy = (int)(e >> 8) - wy0;
-      if ((unsigned)dx < 5u && (unsigned)dy < 5u) A |= 1u << (dy * 5 + dx);
-    }
+// Anomalous cells of the env that fall inside the 5x5 window centred on (cx, cy): bit dy*5+dx.  `sl_s` = shared address of
+// the env's list (8 x uint32, x | y << 16); n (<= 8) is warp-uniform.  Both coordinates are tested with one packed
+// subtraction: u = e + 0x00020002 - (cx | cy << 16) holds dx in its low and dy in its high half (a borrow out of the low
+// half can only happen when dx < 0, i.e. when the entry is rejected anyway); v = 0x00040004 - u; inside <=> no half of u or
+// v is negative.  bit = (u * 0x00010005) >> 16 = dx + 5 dy.
+__device__ __forceinline__ uint32_t anomaly_bit5(uint32_t e, uint32_t cxy) {
+  const uint32_t u = e + 0x00020002u - cxy, v = 0x00040004u - u;
+  return ((u | v) & 0x80008000u) ? 0u : (1u << ((u * 0x00010005u) >> 16));
+}
+__device__ __forceinline__ uint32_t window_anomalies5(uint32_t sl_s, int n, int cx, int cy) {
+  if (n == 0) return 0u;
+  const uint32_t cxy = (uint32_t)cx | ((uint32_t)cy << 16);
+  uint4 a, b = make_uint4(0u, 0u, 0u, 0u);
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "r"(sl_s));
+  uint32_t A = anomaly_bit5(a.x, cxy);
+  if (n > 1) A |= anomaly_bit5(a.y, cxy);
+  if (n > 2) A |= anomaly_bit5(a.z, cxy);
+  if (n > 3) A |= anomaly_bit5(a.w, cxy);
+  if (n > 4) {
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4+16];" : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "r"(sl_s));
+    A |= anomaly_bit5(b.x, cxy);
+    if (n > 5) A |= anomaly_bit5(b.y, cxy);
+    if (n > 6) A |= anomaly_bit5(b.z, cxy);
+    if (n > 7) A |= anomaly_bit5(b.w, cxy);
   }
   return A;
 }
@@ -56,18 +75,29 @@ __device__ __forceinline__ uint32_t window_anomalies5(const uint4 lv, int n, int
 // lo = unmapped & !pad, hi = (anomalous & unmapped) | pad.  `lut_s` = shared address of the 256-entry LUT indexed lo4 | hi4 << 4.
 template <typename OT>
 __device__ __forceinline__ void build_window5(int R, uint32_t sc_s, uint32_t lut_s, uint32_t P, uint32_t A, int wx0, int wy0, OT* st) {
-  int sb = wy0 * R + wx0;   // bit offset of the window's first row in the plane (may be negative)
+  const int sb = wy0 * R + wx0;   // bit offset of the window's first row in the plane (may be negative)
   uint32_t w0[5], w1[5];
-  asm volatile("" ::: "memory");   // the plane reads below stay behind the __syncwarp that publishes this step's clears
-#pragma unroll
-  for (int b = 0; b < 5; ++b) {   // ten independent loads, issued back to back
-    const uint32_t a = sc_s + (uint32_t)(((sb + b * R) >> 5) << 2);
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w0[b]) : "r"(a));
-    asm volatile("ld.shared.b32 %0, [%1+4];" : "=r"(w1[b]) : "r"(a));
-  }
   uint32_t U = 0u;
+  asm volatile("" ::: "memory");   // the plane reads below stay behind the __syncwarp that publishes this step's clears
+  if ((R & 31) == 0) {   // rows are whole words: one address, one shift for all five rows (warp-uniform branch)
+    const uint32_t a = sc_s + (uint32_t)((sb >> 5) << 2), rb = (uint32_t)R >> 3;
 #pragma unroll
-  for (int b = 0; b < 5; ++b) U |= (__funnelshift_r(w0[b], w1[b], (uint32_t)(sb + b * R)) & 31u) << (5 * b);
+    for (int b = 0; b < 5; ++b) {   // ten independent loads, issued back to back
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w0[b]) : "r"(a + b * rb));
+      asm volatile("ld.shared.b32 %0, [%1+4];" : "=r"(w1[b]) : "r"(a + b * rb));
+    }
+#pragma unroll
+    for (int b = 0; b < 5; ++b) U |= (__funnelshift_r(w0[b], w1[b], (uint32_t)sb) & 31u) << (5 * b);
+  } else {
+#pragma unroll
+    for (int b = 0; b < 5; ++b) {
+      const uint32_t a = sc_s + (uint32_t)(((sb + b * R) >> 5) << 2);
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w0[b]) : "r"(a));
+      asm volatile("ld.shared.b32 %0, [%1+4];" : "=r"(w1[b]) : "r"(a));
+    }
+#pragma unroll
+    for (int b = 0; b < 5; ++b) U |= (__funnelshift_r(w0[b], w1[b], (uint32_t)(sb + b * R)) & 31u) << (5 * b);
+  }
   const uint32_t LO = U & ~P, HI = (A & U) | P;
   uint32_t off[7];
 #pragma unroll
@@ -100,7 +130,7 @@ __device__ __forceinline__ void build_window5(int R, uint32_t sc_s, uint32_t lut
 
 // Generic W (any odd size): per-cell, bounds checked.  `sc`: the env's plane, `sl`: its list (shared memory).
 template <typename OT>
-__device__ __forceinline__ void build_window_generic(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* sc, const uint16_t* sl, int cx, int cy,
+__device__ __forceinline__ void build_window_generic(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* sc, const uint32_t* sl, int cx, int cy,
                                                      OT* st) {
   const int W = p.W, h = (W - 1) >> 1;
   for (int b = 0; b < W; ++b)
@@ -111,7 +141,7 @@ __device__ __forceinline__ void build_window_generic(const DevParams& p, const O
         const int cell = gy * p.R + gx;
         code = (sc[cell >> 5] >> (cell & 31)) & 1u;
         if (code) {
-          const uint32_t key = (uint32_t)gx | ((uint32_t)gy << 8);
+          const uint32_t key = (uint32_t)gx | ((uint32_t)gy << 16);
           for (int k = 0; k < p.n_anom; ++k)
             if (sl[k] == key) code = CODE_ANOM;
         }
@@ -123,7 +153,7 @@ __device__ __forceinline__ void build_window_generic(const DevParams& p, const O
 // FULL obs of the group's `nenv` envs from their shared-memory planes through the 16-entry nibble LUT (`lutq`: 4 cells ->
 // one float4 / four bytes), then — after a __syncwarp — the listed anomalous cells that are still unmapped are patched to U.
 template <typename OT>
-__device__ __forceinline__ void emit_full_lut(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* lutq, const uint32_t* sgrid, const uint16_t* slist,
+__device__ __forceinline__ void emit_full_lut(const DevParams& p, const ObsCvt<OT>& cvt, const uint32_t* lutq, const uint32_t* sgrid, const uint32_t* slist,
                                               int nenv, int lane, OT* __restrict__ o) {
   const int RC = p.RC;
   if ((RC & 3) == 0 && ((uintptr_t)o & 15) == 0) {
@@ -147,7 +177,7 @@ __device__ __forceinline__ void emit_full_lut(const DevParams& p, const ObsCvt<O
 // init_env (A2C/noVis_sim.py:36-63) for the env of this tile, built in its shared-memory stage and copied out to HBM.
 // Same RNG spec as reset_tile / oracle_reset_env.  Called by all 32 lanes; `doit` is tile-uniform; q = the lane's new position.
 template <int TS>
-__device__ __forceinline__ void reset_tile_smem(const DevParams& p, int env, int episode, int tl, bool doit, uint32_t* sc, uint16_t* sl, float2& q) {
+__device__ __forceinline__ void reset_tile_smem(const DevParams& p, int env, int episode, int tl, bool doit, uint32_t* sc, uint32_t* sl, float2& q) {
   reset_planes<TS>(p, env, episode, tl, doit, sc, nullptr, sl);
   if (doit) {
     const long long gid = p.env_id_base + env;
@@ -156,6 +186,7 @@ __device__ __forceinline__ void reset_tile_smem(const DevParams& p, int env, int
     for (int w = tl; w < (p.env_words >> 2); w += TS) __stcg(g4 + w, s4[w]);
     if (tl == 0) {
       __stcg(reinterpret_cast<uint4*>(p.alist + (size_t)env * 8), *reinterpret_cast<const uint4*>(sl));
+      __stcg(reinterpret_cast<uint4*>(p.alist + (size_t)env * 8) + 1, *(reinterpret_cast<const uint4*>(sl) + 1));
       p.meta[env] = make_int4(0, p.RC, 0, episode);
     }
     if (tl < p.D) {
@@ -173,13 +204,14 @@ __device__ __forceinline__ void reset_tile_smem(const DevParams& p, int env, int
 // FAST: the production configuration folded at compile time — all four stages in one pass (swarm_step / swarm_rollout),
 //       uint8 actions, collision_dist <= 0.5, no dwell counters, float32-exact coordinates.  FAST = false keeps every switch
 //       at run time (stage entry points, int32/int64 actions, cd > 0.5, dwell, exotic step sizes).
-// LEAN (implies FAST): additionally one step per launch (io.T == 1), N a multiple of the CTA's env count, D == TS, obs and
-//       statistics requested, every per-group array on the TMA path — checked by the host (launch_warp_ts).  Folds the tail /
-//       rollout / alignment bookkeeping of the group loop away; the arithmetic of the four stages is the same code.
+// LEAN (implies FAST): additionally one step per launch (io.T == 1), N a multiple of the warp's env count, D == TS, obs and
+//       statistics requested, every per-group array on the TMA path (16-byte multiples for any whole number of groups) —
+//       checked by the host (launch_warp_ts).  Folds the rollout / alignment bookkeeping of the group loop away; the
+//       arithmetic of the four stages is the same code.
 // The grid is persistent (resident CTAs only): prologue, LUT build and the statistics epilogue are paid once per warp, and
 // the int64[8] statistics cost six RED.ADD per CTA.
 template <int TS, typename OT, int MODE, int WC, bool FAST, bool LEAN = false>
-__global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
+__global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const __grid_constant__ DevParams p, const __grid_constant__ StepIO io) {
   constexpr int EPW = 32 / TS;
   constexpr bool WIN5 = (MODE == 1 && WC == 5);
   constexpr int LUTN = (MODE == 1 ? 256 : 16) * (sizeof(OT) == 4 ? 4 : 1);
@@ -190,6 +222,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   __shared__ unsigned long long s_stats[6];
   __shared__ __align__(16) uint32_t lut[LUTN];    // nibble pair (lo4 | hi4 << 4) -> four cells (float4 / 4 bytes); FULL: lo4 only
   __shared__ uint32_t padx[WIN5 ? 256 : 1], pady[WIN5 ? 256 : 1];   // 5x5 pad masks by centre column / row
+  __shared__ float2 s_dq[8];                      // position delta by action code (noVis_sim.py:121-128)
   const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
   const int wib = __shfl_sync(FULL, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform: group bookkeeping runs on the uniform datapath
   const int flags = FAST ? (F_ALL | (io.flags & F_RESET)) : io.flags;
@@ -202,6 +235,8 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   const int S = p.n_stages;
   if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
   if (threadIdx.x < MAX_STAGES) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x < 8)
+    s_dq[threadIdx.x] = make_float2(threadIdx.x == 1 ? p.ss : (threadIdx.x == 3 ? -p.ss : 0.f), threadIdx.x == 2 ? p.ss : (threadIdx.x == 0 ? -p.ss : 0.f));
   for (int b = threadIdx.x; b < (MODE == 1 ? 256 : 16); b += blockDim.x) {
     if constexpr (sizeof(OT) == 4) reinterpret_cast<float4*>(lut)[b] = cvt.quad(b & 15u, b >> 4);
     else lut[b] = cvt.quad(b & 15u, b >> 4);
@@ -246,29 +281,37 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
   // The two big streams — coverage planes in, observations out — are touched once per step: evict-first keeps them from
   // pushing the small read-modify-write state (positions, meta) out of L2 (measured in round 1: only the pair pays).
   const uint64_t pol_ef = l2_policy_evict_first();
-  const uint32_t in_s = smem_u32(inbuf0), full_s = smem_u32(&full_bar[0]), stage_s = smem_u32(stage), lut_s = smem_u32(lut);
+  const uint32_t in_s = smem_u32(inbuf0), full_s = smem_u32(&full_bar[0]), stage_s = smem_u32(stage), lut_s = smem_u32(lut), cnt_s = smem_u32(&s_cnt[0]);
   const bool pos_tma_c = LEAN ? true : ((EPC * D * 8) & 15) == 0;
   const bool act_tma_c = LEAN ? true : (act_tma_ok && ((EPC * D) & 15) == 0 && io.T == 1);
   const uint32_t cbytes_c = (uint32_t)EPC * (uint32_t)env_words * 4u, posb_c = (uint32_t)EPC * (uint32_t)D * 8u;
-  const uint32_t tx_c = cbytes_c + (uint32_t)EPC * 16u + (pos_tma_c ? posb_c : 0u) + (meta_tma ? (uint32_t)EPC * 16u : 0u) + (act_tma_c ? (uint32_t)(EPC * D) : 0u);
+  const uint32_t tx_c = cbytes_c + (uint32_t)EPC * 32u + (pos_tma_c ? posb_c : 0u) + (meta_tma ? (uint32_t)EPC * 16u : 0u) + (act_tma_c ? (uint32_t)(EPC * D) : 0u);
   // Request the inputs of CTA-group `cg` into stage `s`: up to five bulk copies on full_bar[s] (one thread).  The partial
   // tail CTA-group moves only planes, lists and meta by TMA (their sizes are always multiples of 16 B) and its warps load
   // positions / actions directly.
   auto issue = [&](int cg, int s) {
     const int e0 = cg * EPC;
     const uint32_t dst = in_s + (uint32_t)s * (uint32_t)p.in_bytes, bs = full_s + 8u * (uint32_t)s;
-    if (LEAN || e0 + EPC <= N) {
+    if (LEAN && e0 + EPC > N) {   // the last CTA-group holds fewer (whole) groups: every size stays a multiple of 16 B
+      const uint32_t ne = (uint32_t)(N - e0);
+      mbar_expect_tx_s(bs, ne * ((uint32_t)env_words * 4u + 32u + (uint32_t)D * 8u + 16u + (uint32_t)D));
+      bulk_g2s_s_hint(dst, p.cov + (size_t)e0 * env_words, ne * (uint32_t)env_words * 4u, bs, pol_ef);
+      bulk_g2s_s(dst + p.off_alist, p.alist + (size_t)e0 * 8, ne * 32u, bs);
+      bulk_g2s_s(dst + p.off_pos, p.pos + (size_t)e0 * D, ne * (uint32_t)D * 8u, bs);
+      bulk_g2s_s(dst + p.off_meta, p.meta + e0, ne * 16u, bs);
+      bulk_g2s_s(dst + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, ne * (uint32_t)D, bs);
+    } else if (LEAN || e0 + EPC <= N) {
       mbar_expect_tx_s(bs, tx_c);
       bulk_g2s_s_hint(dst, p.cov + (size_t)e0 * env_words, cbytes_c, bs, pol_ef);
-      bulk_g2s_s(dst + p.off_alist, p.alist + (size_t)e0 * 8, (uint32_t)EPC * 16u, bs);
+      bulk_g2s_s(dst + p.off_alist, p.alist + (size_t)e0 * 8, (uint32_t)EPC * 32u, bs);
       if (pos_tma_c) bulk_g2s_s(dst + p.off_pos, p.pos + (size_t)e0 * D, posb_c, bs);
       if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, (uint32_t)EPC * 16u, bs);
       if (act_tma_c) bulk_g2s_s(dst + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, (uint32_t)(EPC * D), bs);
     } else {
       const uint32_t ne = (uint32_t)(N - e0);
-      mbar_expect_tx_s(bs, ne * (uint32_t)env_words * 4u + ne * 16u + (meta_tma ? ne * 16u : 0u));
+      mbar_expect_tx_s(bs, ne * (uint32_t)env_words * 4u + ne * 32u + (meta_tma ? ne * 16u : 0u));
       bulk_g2s_s(dst, p.cov + (size_t)e0 * env_words, ne * (uint32_t)env_words * 4u, bs);
-      bulk_g2s_s(dst + p.off_alist, p.alist + (size_t)e0 * 8, ne * 16u, bs);
+      bulk_g2s_s(dst + p.off_alist, p.alist + (size_t)e0 * 8, ne * 32u, bs);
       if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, ne * 16u, bs);
     }
   };
@@ -301,17 +344,18 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
       if (cg < 0) break;
     }
     const int grp = cg * wpb + wib;
-    if (LEAN || grp < ngroups) {
+    if (grp < ngroups) {
     unsigned char* const in = inbuf0 + s * p.in_bytes;
     uint32_t* const sgrid = reinterpret_cast<uint32_t*>(in) + wib * EPW * env_words;          // the group's planes
-    uint16_t* const slist = reinterpret_cast<uint16_t*>(in + p.off_alist) + wib * EPW * 8;     // the group's lists
+    uint32_t* const slist = reinterpret_cast<uint32_t*>(in + p.off_alist) + wib * EPW * 8;     // the group's lists
     const bool cta_full = LEAN ? true : (cg * EPC + EPC <= N);
     const int env0 = grp * EPW, nenv = LEAN ? EPW : min(EPW, N - env0);
     const bool valid = LEAN ? true : (tile < nenv);
     const int env = valid ? env0 + tile : env0;
     const bool active = LEAN ? true : (valid && tl < D);
     uint32_t* const sc = sgrid + tile * env_words;
-    uint16_t* const sl = slist + tile * 8;
+    uint32_t* const sl = slist + tile * 8;
+    const uint32_t sl_s = in_s + (uint32_t)s * (uint32_t)p.in_bytes + (uint32_t)p.off_alist + (uint32_t)((wib * EPW + tile) * 32);
     const uint32_t sc_s = in_s + (uint32_t)s * (uint32_t)p.in_bytes + (uint32_t)((wib * EPW + tile) * env_words) * 4u;
     uint32_t* const gc = p.cov + (size_t)env * env_words;
     const bool pos_tma = pos_tma_c && cta_full, act_tma = act_tma_c && cta_full;
@@ -335,17 +379,15 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
 
       // ---- stage (1): action decode + move + clip (noVis_sim.py:117-135)
       if (active && (flags & F_MOVE)) {
-        float sx = (a == 1) ? p.ss : 0.f, sy = (a == 2) ? p.ss : 0.f;   // a=0: y-=ss, 1: x+=ss, 2: y+=ss, 3: x-=ss
-        sx = (a == 3) ? -p.ss : sx;
-        sy = (a == 0) ? -p.ss : sy;
         if ((unsigned)a > 3u) atomicOr(p.err, 1);
-        q.x = fminf(fmaxf(q.x + sx, 0.f), p.xmax);
-        q.y = fminf(fmaxf(q.y + sy, 0.f), p.ymax);
+        const float2 dq = s_dq[(unsigned)a > 3u ? 4 : a];   // a=0: y-=ss, 1: x+=ss, 2: y+=ss, 3: x-=ss; anything else: no move
+        q.x = fminf(fmaxf(q.x + dq.x, 0.f), p.xmax);
+        q.y = fminf(fmaxf(q.y + dq.y, 0.f), p.ymax);
         __stcg(pp, q);
       }
       int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);   // nearest lattice cell = window centre
       uint32_t A = 0u;                                                    // WIN5: anomalous cells inside the drone's window
-      if constexpr (WIN5) A = window_anomalies5(*reinterpret_cast<const uint4*>(sl), p.n_anom, cx - 2, cy - 2);
+      if constexpr (WIN5) A = window_anomalies5(sl_s, p.n_anom, cx, cy);
 
       // ---- stage (2): coverage scatter on the shared-memory plane
       int rew = 0, ncl = 0, an_w = 0;
@@ -392,7 +434,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
             int an;
             if constexpr (WIN5) an = (int)((A >> 12) & 1u);   // the window's centre cell
             else {
-              const uint32_t key = (uint32_t)cx | ((uint32_t)cy << 8);
+              const uint32_t key = (uint32_t)cx | ((uint32_t)cy << 16);
               an = 0;
               for (int k = 0; k < p.n_anom; ++k) an |= (sl[k] == key) ? 1 : 0;
             }
@@ -466,7 +508,7 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
             const int episode = __shfl_sync(FULL, m.w, lead);   // already the new episode index where do_reset
             reset_tile_smem<TS>(p, env, episode, tl, do_reset, sc, sl, q);
             cx = (int)floorf(q.x + 0.5f); cy = (int)floorf(q.y + 0.5f);
-            if constexpr (WIN5) A = window_anomalies5(*reinterpret_cast<const uint4*>(sl), p.n_anom, cx - 2, cy - 2);
+            if constexpr (WIN5) A = window_anomalies5(sl_s, p.n_anom, cx, cy);
           }
         }
       } else if (flags & F_SCATTER) {   // staged scatter (swarm_stage_scatter)
@@ -484,20 +526,24 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
         } else {
           if (lane == 0) bulk_wait_read0();   // the previous bulk store has drained `stage` (long ago)
           __syncwarp();
+#ifndef SWARM_EXP_NOWINDOW   // experiment build: the obs stream without the window arithmetic
           if (active) {
             if constexpr (WIN5) build_window5<OT>(p.R, sc_s, lut_s, padx[cx] | pady[cy], A, cx - 2, cy - 2, my_stage);
             else build_window_generic<OT>(p, cvt, sc, sl, cx, cy, my_stage);
           }
+#endif
           fence_proxy_async();   // generic-proxy writes to `stage` ordered before the async-proxy read below
           __syncwarp();
           const int n = nenv * D * WW;
           OT* dst = obase + (size_t)env0 * D * WW;
           const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(OT);
           if (LEAN || ((((uintptr_t)dst) & 15) == 0 && (bytes & 15u) == 0)) {
+#ifndef SWARM_EXP_NOSTORE   // experiment build: everything but the obs stream (what the compute side alone costs)
             if (lane == 0) {   // one TMA bulk store for the whole group
               bulk_s2g_s_hint(dst, stage_s, bytes, pol_ef);
               bulk_commit();
             }
+#endif
           } else {
             for (int k = lane; k < n; k += 32) __stcs(dst + k, stage[k]);
           }
@@ -506,11 +552,15 @@ __global__ void __launch_bounds__(256, SWARM_MINB) step_warp_kernel(const __grid
       __syncwarp();
     }
     }   // grp < ngroups
-    // leave the stage; the last warp out refills it with the CTA-group S iterations ahead
-    fence_proxy_async();   // this group's generic accesses to the stage precede the bulk copies that refill it
-    __syncwarp();
+    // leave the stage; the last warp out refills it with the CTA-group S iterations ahead.  This group's generic accesses
+    // to the stage must precede the bulk copies that refill it: in the LEAN WINDOW kernel the proxy fence + __syncwarp issued
+    // before the obs bulk store already follows the last of them.
+    if (!(LEAN && MODE == 1)) {
+      fence_proxy_async();
+      __syncwarp();
+    }
     if (lane == 0) {
-      if (atomicAdd(&s_cnt[s], 1) == wpb - 1) {
+      if ((int)smem_atomic_inc(cnt_s + 4u * (uint32_t)s) == wpb - 1) {
         s_cnt[s] = 0;
         refill(it + S, s);
       }
