@@ -425,10 +425,22 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io_in, cudaStream_t
       default: err = launch_warp_ts<32, OT>(e, io, st, blocks, smem); break;
     }
   } else {
-    // one CTA per env; the env's packed grid is staged in shared memory when it fits (160 KB = 640k cells)
-    const long long need = (long long)p.env_words * 4 * (p.list_mode ? 1 : 2) + 64;
-    const int staged = need <= 160 * 1024;
-    const int smem = staged ? (int)need : 0;
+    // one CTA per env; the env's plane(s) are staged in shared memory when they fit (160 KB), plus — WINDOW obs of W == 5
+    // in LIST mode — a staging image of the env's [D][25] obs block (staged == 2).  WINDOW obs: CTAs of one thread per drone
+    // (64 threads for cfg5b, ~7 envs resident per SM); FULL obs: 256 threads stream the 256 KiB of a 256 x 256 env.
+    const long long planes = (long long)p.env_words * 4 * (p.list_mode ? 1 : 2);
+    const long long image = (p.list_mode && p.obs_mode == SWARM_OBS_WINDOW && p.W == 5 && p.D <= 255)
+                                ? (long long)p.D * 25 * (p.obs_dtype == SWARM_DTYPE_F32 ? 4 : 1) : 0;
+    int staged = planes + 64 <= 160 * 1024 ? 1 : 0;
+    long long need = staged ? planes + 64 : 0;
+    if (staged && image && planes + 64 + image + 16 <= 200 * 1024) { staged = 2; need = planes + 64 + image + 16; }
+    const int smem = (int)need;
+    int threads = 256;
+    if (p.obs_mode == SWARM_OBS_WINDOW) {
+      threads = (p.D + 31) / 32 * 32;
+      if (threads < 64) threads = 64;
+      if (threads > 256) threads = 256;
+    }
     static int cta_limit[64] = {0};   // per-function limit, only raised (see launch_warp_inst)
     int& limit = cta_limit[e->cfg.device & 63];
     if (smem > limit) {
@@ -437,12 +449,12 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io_in, cudaStream_t
     }
     if (!e->resident[0]) {
       int per_sm = 0;
-      if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_cta_kernel<OT>, 256, smem)) != cudaSuccess) return err;
+      if ((err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_cta_kernel<OT>, threads, smem)) != cudaSuccess) return err;
       e->resident[0] = (per_sm > 0 ? per_sm : 1) * e->sm_count;
     }
     long long blocks = p.N;
     if (blocks > e->resident[0]) blocks = e->resident[0];   // resident CTAs only, grid-stride beyond
-    step_cta_kernel<OT><<<(int)blocks, 256, smem, st>>>(p, io, staged);
+    step_cta_kernel<OT><<<(int)blocks, threads, smem, st>>>(p, io, staged);
   }
   e->launches++;
   return err;

@@ -12,6 +12,7 @@
 #include "swarm_common.cuh"
 #include "swarm_emit.cuh"
 #include "swarm_step.cuh"
+#include "swarm_window.cuh"
 
 namespace swarm {
 
@@ -241,6 +242,10 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   __shared__ int s_pk, s_reset;
   __shared__ __align__(16) uint32_t s_list[8];
   __shared__ float2 s_pos[256];   // this step's positions of the env (wide path): spread test and window emission read them here
+  // W == 5 window fast path (LIST mode, wide path): the tables of swarm_window.cuh, and a staging image of the env's
+  // [D][25] obs block behind the plane in dynamic shared memory, streamed out with ONE TMA bulk store per env
+  __shared__ __align__(16) uint32_t lut[256 * (sizeof(OT) == 4 ? 4 : 1)];
+  __shared__ uint32_t padx[256], pady[256];
   CtaView v;
   v.sc = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
   v.sa = (staged && !p.list_mode) ? reinterpret_cast<const uint32_t*>(cta_smem) + p.env_words : nullptr;
@@ -267,7 +272,15 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   };
   // production path: stages (1)-(2) on all threads, one drone per thread (30 * 255 < 2^16 keeps the packed totals exact)
   const bool wide = staged && (flags & (F_MOVE | F_SCATTER | F_REWARD)) == (F_MOVE | F_SCATTER | F_REWARD) && p.cd_fast && !p.has_wait &&
-                    p.D <= 255 && p.D < (int)blockDim.x;
+                    p.D <= 255 && p.D <= (int)blockDim.x;
+  const uint32_t win_bytes = (uint32_t)p.D * 25u * (uint32_t)sizeof(OT);
+  const bool win5 = wide && want_obs && p.list_mode && p.obs_mode == 1 && p.W == 5 && (win_bytes & 15u) == 0u && staged == 2;
+  OT* const s_win = reinterpret_cast<OT*>(cta_smem + (((size_t)p.env_words * 4 + 15) & ~(size_t)15));   // staged == 2: room behind the plane
+  if (win5) {
+    const ObsCvt<OT> cvt(p);
+    build_window_tables<OT>(p, cvt, lut, 256, padx, pady, threadIdx.x, blockDim.x);
+    __syncthreads();
+  }
   for (int env = blockIdx.x; env < p.N; env += gridDim.x) {
     int4 m_pre = make_int4(0, 0, 0, 0);
     if (staged && threadIdx.x == 0) {
@@ -310,7 +323,27 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
       }
       if (want_obs && (!io.obs_last_only || t == io.T - 1)) {
         OT* o = reinterpret_cast<OT*>(io.obs_out) + (io.obs_last_only ? (size_t)0 : (size_t)t * p.N * p.obs_per_env);
-        if (staged) emit_obs_cta_smem<OT>(p, v, env, threadIdx.x, blockDim.x, o, (stepping && wide) ? s_pos : nullptr);
+        if (win5) {   // one thread per drone builds its window into the staging image; one bulk store per env
+          if (threadIdx.x == 0) bulk_wait_read0();   // the previous env's / step's bulk store has drained the image
+          __syncthreads();
+          if ((int)threadIdx.x < p.D) {
+            const float2 q = s_pos[threadIdx.x];
+            const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
+            const uint32_t A = window_anomalies5(smem_u32(s_list), p.n_anom, cx, cy);
+            build_window5<OT>(p.R, smem_u32(v.sc), smem_u32(lut), padx[cx] | pady[cy], A, cx - 2, cy - 2, s_win + (size_t)threadIdx.x * 25);
+          }
+          fence_proxy_async();   // generic-proxy writes to the image ordered before the async-proxy read below
+          __syncthreads();
+          OT* dst = o + (size_t)env * p.D * 25;
+          if (threadIdx.x == 0) {
+            if ((((uintptr_t)dst) & 15) == 0) {
+              bulk_s2g(dst, s_win, win_bytes);
+              bulk_commit();
+            } else {
+              for (uint32_t k = 0; k < (uint32_t)p.D * 25u; ++k) dst[k] = s_win[k];
+            }
+          }
+        } else if (staged) emit_obs_cta_smem<OT>(p, v, env, threadIdx.x, blockDim.x, o, (stepping && wide) ? s_pos : nullptr);
         else emit_obs_global<OT>(p, env, threadIdx.x, blockDim.x, o);
       }
       if (t + 1 < io.T) __syncthreads();   // emission reads precede the next step's clears; s_reset is re-armed
@@ -321,6 +354,7 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
     }
   }
 
+  if (win5 && threadIdx.x == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
   if (io.stats && (flags & F_REWARD)) {   // only warp 0 accumulated
     if (warp == 0) {
       long long vv[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
