@@ -620,7 +620,92 @@ def measure_e2e(torch, dist, dev, world, env, acts_host, obs_dt, E):
     return ms, d2h
 
 
-def measure_strong(torch, dist, dev, world, rank, kw, total_envs, args, value_1gpu, ms_step_1gpu, weak_loop):
+def measure_rollout(torch, dist, dev, world, envs, acts, T, D, per, bytes_env, peak, steps_target, use_graph):
+    """swarm_rollout: T env steps per launch from actions[T, N, D], observations of every step written to obs[T, N, ...]
+    (coverage, positions and meta stay on chip between the T steps).  One CUDA graph of 2 rollouts per env batch, replayed;
+    device-timed, max over ranks."""
+    acts_T = acts[:T].contiguous() if T <= acts.shape[0] else acts.repeat((T + acts.shape[0] - 1) // acts.shape[0], 1, 1)[:T].contiguous()
+    obs_T = torch.empty((T,) + tuple(envs[0].obs_shape), dtype=envs[0].obs_dtype, device=dev)
+    rew_T = torch.empty((T, per), dtype=torch.float32, device=dev)
+    done_T = torch.empty((T, per), dtype=torch.uint8, device=dev)
+
+    def rollouts():
+        for _ in range(2):
+            for e in envs:
+                e.rollout(acts_T, obs_out=obs_T, reward_out=rew_T, done_out=done_T)
+    rollouts()
+    torch.cuda.synchronize(dev)
+    g = None
+    if use_graph:
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                rollouts()
+            g.replay()
+            torch.cuda.synchronize(dev)
+        except Exception as exc:
+            print(f"[bench] rollout graph capture failed ({exc!r}); eager", file=sys.stderr)
+            g = None
+    if world > 1:
+        flag = torch.tensor([1 if g is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            g = None
+    steps_per = 2 * len(envs) * T
+    reps = max(1, steps_target // steps_per)
+    stream = torch.cuda.current_stream(dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record(stream)
+    for _ in range(reps):
+        g.replay() if g is not None else rollouts()
+    t1.record(stream)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    msr = t0.elapsed_time(t1)
+    if world > 1:
+        t = torch.tensor([msr], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        msr = float(t.item())
+    usr = msr / (reps * steps_per) * 1e3
+    out = {"us_per_step": usr, "value": float(per) * world * D / (usr * 1e-6), "unit": UNIT,
+           "roofline_frac": bytes_env * per / (usr * 1e-6) / 1e9 / peak, "steps": reps * steps_per, "rollout_T": T,
+           "launch": ("CUDA graph of " if g is not None else "eager: ") + f"{2 * len(envs)} swarm_rollout(T={T}) launches, obs of every step written",
+           "obs_buffer_mb": obs_T.numel() * obs_T.element_size() / 1e6}
+    if g is not None:
+        g.reset()
+    del obs_T
+    return out
+
+
+def launch_floor_us(torch, dev, n=32, reps=20):
+    """Step-to-step time of a CUDA graph of n dependent launches of a one-element kernel: what ANY one-launch-per-step loop
+    pays per step on this box before doing work (context for the small workloads' roofline fractions)."""
+    x = torch.zeros(1, device=dev)
+    for _ in range(3):
+        x.add_(1.0)
+    torch.cuda.synchronize(dev)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(n):
+            x.add_(1.0)
+    g.replay()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(reps):
+        g.replay()
+    t1.record()
+    torch.cuda.synchronize(dev)
+    us = t0.elapsed_time(t1) / (n * reps) * 1e3
+    g.reset()
+    return us
+
+
+def measure_strong(torch, dist, dev, world, rank, kw, total_envs, args, value_1gpu, ms_step_1gpu, weak_loop, rollout_1gpu):
     """Strong scaling of the workload: `total_envs` envs sharded over the ranks (contiguous env-id ranges, no data-path
     collective).  Two launch forms, both timed on the device as the max over ranks:
       single-step: one swarm_step launch per env step, 32 of them per CUDA graph (the policy-in-the-loop form);
@@ -631,7 +716,7 @@ def measure_strong(torch, dist, dev, world, rank, kw, total_envs, args, value_1g
     per = total_envs // world
     bytes_env = algorithmic_bytes_per_env_step(kw)
     peak, _ = load_peak()
-    out = {"total_envs": per * world, "envs_per_gpu": per, "scaling": "strong", "rollout_T": args.rollout_T}
+    out = {"total_envs": per * world, "envs_per_gpu": per, "scaling": "strong"}
     Ks = max(32, args.strong_steps // 32 * 32)
     if world == 1:
         loop, own = weak_loop, False
@@ -659,64 +744,11 @@ def measure_strong(torch, dist, dev, world, rank, kw, total_envs, args, value_1g
     us = ms / Ks * 1e3
     out["single_step"] = {"us_per_step": us, "value": float(per) * world * D / (us * 1e-6), "unit": UNIT,
                           "roofline_frac": bytes_env * per / (us * 1e-6) / 1e9 / peak, "steps": Ks, "env_batches_rotated": sets_s}
-    # rollout form: T steps per launch, one graph of 2 rollouts per env batch
-    T = max(1, args.rollout_T)
-    envs = loop.envs
-    acts_T = loop.acts[:T].contiguous() if T <= loop.N_ACT else loop.acts.repeat((T + 31) // 32, 1, 1)[:T].contiguous()
-    obs_T = torch.empty((T,) + tuple(envs[0].obs_shape), dtype=torch.float32, device=dev)
-    rew_T = torch.empty((T, per), dtype=torch.float32, device=dev)
-    done_T = torch.empty((T, per), dtype=torch.uint8, device=dev)
-
-    def rollouts():
-        for _ in range(2):
-            for e in envs:
-                e.rollout(acts_T, obs_out=obs_T, reward_out=rew_T, done_out=done_T)
-    rollouts()
-    torch.cuda.synchronize(dev)
-    g = None
-    if not args.no_graph:
-        try:
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                rollouts()
-            g.replay()
-            torch.cuda.synchronize(dev)
-        except Exception as exc:
-            print(f"[bench] rollout graph capture failed ({exc!r}); eager", file=sys.stderr)
-            g = None
-    if world > 1:
-        flag = torch.tensor([1 if g is not None else 0], device=dev)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        if int(flag.item()) == 0:
-            g = None
-    steps_per = 2 * len(envs) * T
-    reps = max(1, Ks // steps_per)
-    stream = torch.cuda.current_stream(dev)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize(dev)
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0.record(stream)
-    for _ in range(reps):
-        g.replay() if g is not None else rollouts()
-    t1.record(stream)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-    msr = t0.elapsed_time(t1)
-    if world > 1:
-        t = torch.tensor([msr], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        msr = float(t.item())
-    usr = msr / (reps * steps_per) * 1e3
-    out["rollout"] = {"us_per_step": usr, "value": float(per) * world * D / (usr * 1e-6), "unit": UNIT,
-                      "roofline_frac": bytes_env * per / (usr * 1e-6) / 1e9 / peak, "steps": reps * steps_per,
-                      "launch": ("CUDA graph of " if g is not None else "eager: ") + f"{2 * len(envs)} swarm_rollout(T={T}) launches, obs of every step written",
-                      "obs_buffer_mb": obs_T.numel() * 4 / 1e6}
-    del obs_T
+    out["rollout"] = rollout_1gpu if world == 1 else measure_rollout(torch, dist, dev, world, loop.envs, loop.acts, max(1, args.rollout_T), D,
+                                                                     per, bytes_env, peak, Ks, not args.no_graph)
     if own:
         loop.close()
-        for e in envs:
+        for e in loop.envs:
             e.close()
     return out
 
@@ -741,6 +773,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-strong", action="store_true", help="skip the extra strong-scaling measurement of the default cfg3 line")
     ap.add_argument("--strong-steps", type=int, default=256)
+    ap.add_argument("--no-rollout", action="store_true", help="skip the swarm_rollout(T) measurement of the workload")
     ap.add_argument("--rollout-T", type=int, default=16, help="strong scaling: env steps per swarm_rollout launch")
     ap.add_argument("--stats-mode", default="peer", choices=["peer", "nccl"],
                     help="N > 1: how the per-step episode statistics cross GPUs — 'peer': pushed by the step kernel into "
@@ -872,13 +905,21 @@ def main():
     total_agent_steps = float(n_envs) * D * K * world
     value = total_agent_steps / (ms_total * 1e-3)
 
+    # ---- the same workload through swarm_rollout (T steps per launch) and the box's per-launch floor: context for the
+    # one-launch-per-step value above, most of all for the small workloads (cfg2 / cfg4 / cfg5b move ~10 MB per step)
+    rollout = None
+    if not args.no_rollout:
+        peak_r, _ = load_peak()
+        rollout = measure_rollout(torch, dist, dev, world, envs, loop.acts, max(1, args.rollout_T), D, n_envs,
+                                  algorithmic_bytes_per_env_step(kw, s_o=s_o), peak_r, 256, not args.no_graph)
     # ---- strong scaling of the same workload (BASELINE configs[2]: "65536 envs ... sharded over 1/2/4/8"): the workload's env
     # count divided over the ranks, contiguous env-id ranges, measured next to the weak-scaling value above
     strong = None
     if args.workload == "cfg3" and args.scaling == "weak" and not args.no_strong and not args.envs and args.obs_dtype == "float32":
         strong = measure_strong(torch, dist, dev, world, rank, kw, workload_envs, args, value if world == 1 else None,
-                                ms_total / K if world == 1 else None, loop)
+                                ms_total / K if world == 1 else None, loop, rollout)
 
+    floor_us = launch_floor_us(torch, dev)
     # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region).
     # Headline format: uint8 observations (values 0 / 1 / U, pad 255) — the reference's obs are small integers (int64 on the
     # host, A2C/noVis_sim.py:168-170) that its callers cast to float32 themselves (A2C/train.py:21-24), so a byte per cell is
@@ -953,6 +994,7 @@ def main():
             "e2e_float32_obs": {"value": agent_e2e / (ef_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": ef_d2h,
                                 "steps": E, "ms_per_step": ef_ms / E, "obs_format": "float32 (what the reference's callers cast to)",
                                 "d2h_gbs_per_rank": ef_d2h / (ef_ms / E * 1e-3) / 1e9},
+            "rollout": rollout, "launch_floor_us": floor_us,
             "strong_scaling": strong,
             "stats_check": stats_check, "stats_global_env_batch0": stats_global,
             "gpu_launches": launches, "clocks": dict(clocks, window=f"{hold * n_act} untimed steps + the {K} timed steps, continuous load"),
