@@ -31,7 +31,8 @@
  *  - dwell counters     int16 [N][C][R]   only when dwell_normal|dwell_anom != 0
  *  - obs FULL           T     [N][R*C]    obs[n][y*R+x]                (T = float32 or uint8)
  *  - obs WINDOW         T     [N][D][W*W] win[n][i][b*W+a] = grid[cx-h+a][cy-h+b], pad -1 (255 for uint8)
- *  - resident grid (private) is 2 bits / cell, 16 cells per uint32, flat index y*R+x.
+ *  - resident coverage map (private): 1 bit / cell (1 = still unmapped), 32 cells per uint32, flat index y*R+x, plus the
+ *    env's anomalous cells as a list of 8 x uint32 (x | y << 16) or, for more than 8 anomalies / sides > 256, a second plane.
  */
 #ifndef SWARM_B200_H_
 #define SWARM_B200_H_
@@ -61,7 +62,8 @@ enum { SWARM_DTYPE_F32 = 0, SWARM_DTYPE_U8 = 1 };      /* obs element type */
 enum { SWARM_ACT_U8 = 0, SWARM_ACT_I32 = 1, SWARM_ACT_I64 = 2 };
 
 /* device error word bits (sticky until swarm_device_error(clear=1)) */
-enum { SWARM_DEVERR_BAD_ACTION = 1, SWARM_DEVERR_STATS_TIMEOUT = 4 };
+enum { SWARM_DEVERR_BAD_ACTION = 1, SWARM_DEVERR_STATS_TIMEOUT = 4,
+       SWARM_DEVERR_BAD_STATE = 8 /* swarm_set_state: more cells of value U than n_anamolous */ };
 
 /* statistics vector, int64[8], accumulated with atomics */
 enum {
@@ -121,7 +123,7 @@ int64_t swarm_obs_elems(const SwarmEnv* env);
 int64_t swarm_obs_bytes(const SwarmEnv* env);
 
 /* Device pointers into the resident state (views stay valid until swarm_destroy):
- * which = 0: positions float[N][D][2]; 1: meta int32[N][4]; 2: packed grid uint32[N][env_words];
+ * which = 0: positions float[N][D][2]; 1: meta int32[N][4]; 2: coverage bit plane uint32[N][env_words];
  * 3: device error word int32[1]; 4: internal statistics int64[8]. */
 int swarm_state_ptr(SwarmEnv* env, int which, void** ptr_out, int64_t* bytes_out);
 
