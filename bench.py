@@ -537,6 +537,35 @@ class StepLoop:
                 return None
         return self.graphs[n]
 
+    def timed_graph(self, n, tail=None):
+        """A graph of [record e0][steps 0 .. n-1][record e1] with EXTERNAL timing events (cudaEventRecordExternal nodes): the
+        elapsed time between the two nodes is the device time of exactly n steps, without the host's graph-launch latency that
+        an event pair around a single short replay would include.  Returns (graph, e0, e1) or None."""
+        torch = self.torch
+        if not self.use_graph or n <= 0:
+            return None
+        try:
+            e0 = torch.cuda.Event(enable_timing=True, external=True)
+            e1 = torch.cuda.Event(enable_timing=True, external=True)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                e0.record(torch.cuda.current_stream(self.dev))
+                for j in range(n):
+                    self.one_step(j)
+                if tail is not None:
+                    tail()
+                e1.record(torch.cuda.current_stream(self.dev))
+            g.replay()
+            torch.cuda.synchronize(self.dev)
+            if not (e0.elapsed_time(e1) > 0):
+                raise RuntimeError("external events did not time")
+            self.graphs[("timed", n)] = g
+            return g, e0, e1
+        except Exception as exc:
+            print(f"[bench] timed graph with external events unavailable ({exc!r}); timing around the replay", file=sys.stderr)
+            torch.cuda.synchronize(self.dev)
+            return None
+
     def plan(self, count, tail=None):
         """(full replays, remainder) of `count` steps and the graphs they need; eager when graphs are off."""
         full, rem = divmod(count, self.N_ACT)
@@ -571,22 +600,30 @@ class StepLoop:
         self.graphs = {}
 
 
-def time_steps(torch, dist, dev, world, loop, K, plan, tail_sync=None):
-    """Device time of exactly K steps, bracketed by barrier + synchronize, max over ranks (ms)."""
+def time_steps(torch, dist, dev, world, loop, K, plan, tail_sync=None, timed=None):
+    """Device time of exactly K steps, bracketed by barrier + synchronize, max over ranks (ms).  `timed` = (graph, e0, e1) of
+    StepLoop.timed_graph: the events are nodes of the replayed graph itself (used when the whole region is ONE short graph)."""
     stream = torch.cuda.current_stream(dev)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0.record(stream)
-    loop.run(K, plan)
-    if tail_sync is not None:
-        tail_sync()
-    t1.record(stream)
-    torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier()
-    ms = t0.elapsed_time(t1)
+    if timed is not None:
+        timed[0].replay()
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        ms = timed[1].elapsed_time(timed[2])
+    else:
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record(stream)
+        loop.run(K, plan)
+        if tail_sync is not None:
+            tail_sync()
+        t1.record(stream)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        ms = t0.elapsed_time(t1)
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -867,6 +904,14 @@ def main():
         if int(flag.item()) == 0:
             plan = hold_plan = None
 
+    # K <= 32: the whole timed region is one short graph — time it between event nodes INSIDE the graph, so the host's
+    # graph-launch latency (~15 us against a 0.6 ms region at the driver's --steps 20) is not booked as kernel time
+    timed = loop.timed_graph(K, tail) if (plan is not None and K <= n_act) else None
+    if world > 1:
+        flag = torch.tensor([1 if timed is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            timed = None
     # The timed region of a microsecond-scale step lasts milliseconds, shorter than nvidia-smi's sampling period, so the
     # clock sampler runs over a window of identical untimed steps that leads straight into the K timed ones
     # (continuous load, no idle gap); the window is named in the JSON.
@@ -883,7 +928,7 @@ def main():
     hold = int(min(40000, max(0, args.clock_window_s / est))) // n_act
     for _ in range(hold):
         loop.run(n_act, hold_plan)
-    ms_total = time_steps(torch, dist, dev, world, loop, K, plan, tail)
+    ms_total = time_steps(torch, dist, dev, world, loop, K, plan, tail, timed)
     clocks = sampler.stop() if rank == 0 else None
     launches = K                            # one step kernel per step (graph replays launch the captured kernels)
     # a second, longer graph-replayed region (diagnostic: shows that `value` does not depend on --steps)
@@ -983,7 +1028,7 @@ def main():
                          "kernel_ms_avg": kern_avg_ms, "kernel_ms_avg_how": "timed region / steps: the stream holds only step kernels back to back under graph replay",
                          "kernel_ms_event_pairs_avg": pair_avg_ms, "kernel_ms_event_pairs_median": kern_ms[len(kern_ms) // 2],
                          "kernel_ms_event_pairs_how": "separate EAGER pass, one CUDA-event pair per launch (diagnostic; includes Python launch gaps)",
-                         "launch": loop.describe(K, plan),
+                         "launch": loop.describe(K, plan) + (" (timed between event nodes inside the graph)" if timed is not None else ""),
                          "ms_per_step_1024_steps": ms_long / K_long,
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "algorithmic_bytes_per_agent_step": algorithmic_bytes_per_env_step(kw, s_o=s_o) / D},
