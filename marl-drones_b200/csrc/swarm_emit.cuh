@@ -83,7 +83,9 @@ __device__ __forceinline__ void emit_full_patch(const DevParams& p, const ObsCvt
   for (int v = tid; v < nenv * na; v += nthr) {
     const int e = v / na, k = v - e * na;
     const uint32_t key = sl[e * 8 + k];
-    const int cell = (int)(key >> 16) * p.R + (int)(key & 0xffffu);
+    const int x = (int)(key & 0xffffu), y = (int)(key >> 16);
+    if (x >= p.R || y >= p.C) continue;   // LIST_EMPTY: an injected state with no anomalous cell to name (set_state_kernel)
+    const int cell = y * p.R + x;
     if ((sc[e * p.env_words + (cell >> 5)] >> (cell & 31)) & 1u) o[(size_t)e * p.RC + cell] = cvt.one(CODE_ANOM);
   }
 }

@@ -178,7 +178,11 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
       bulk_g2s_s(dst + p.off_act, (const uint8_t*)io.actions + (size_t)e0 * D, ne * (uint32_t)D, bs);
     } else if (LEAN || e0 + EPC <= N) {
       mbar_expect_tx_s(bs, tx_c);
+#ifdef SWARM_EXP_NOHINT_LD
+      bulk_g2s_s(dst, p.cov + (size_t)e0 * env_words, cbytes_c, bs);
+#else
       bulk_g2s_s_hint(dst, p.cov + (size_t)e0 * env_words, cbytes_c, bs, pol_ef);
+#endif
       bulk_g2s_s(dst + p.off_alist, p.alist + (size_t)e0 * 8, (uint32_t)EPC * 32u, bs);
       if (pos_tma_c) bulk_g2s_s(dst + p.off_pos, p.pos + (size_t)e0 * D, posb_c, bs);
       if (meta_tma) bulk_g2s_s(dst + p.off_meta, p.meta + e0, (uint32_t)EPC * 16u, bs);
@@ -201,7 +205,11 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
       s_cg[s] = cg;
       if (cg < 0) { mbar_arrive_s(full_s + 8u * (uint32_t)s); return; }
     } else {
+#ifdef SWARM_EXP_BLOCKED
+      { const int per = (ncg + (int)gridDim.x - 1) / (int)gridDim.x; cg = (k < per) ? (int)blockIdx.x * per + k : ncg; }
+#else
       cg = (int)blockIdx.x + k * (int)gridDim.x;
+#endif
       if (cg >= ncg) return;
     }
     issue(cg, s);
@@ -212,7 +220,12 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
   uint32_t par = 0u;   // parity of the current use of the stages (flips every S iterations)
   int s = 0;
   for (int it = 0;; ++it) {
+#ifdef SWARM_EXP_BLOCKED
+    const int per_b = (ncg + (int)gridDim.x - 1) / (int)gridDim.x;
+    int cg = (it < per_b) ? (int)blockIdx.x * per_b + it : ncg;
+#else
     int cg = (int)blockIdx.x + it * (int)gridDim.x;
+#endif
     if (!dyn && cg >= ncg) break;
     mbar_wait_s(full_s + 8u * (uint32_t)s, par);
     if (dyn) {
@@ -416,7 +429,11 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
           if (LEAN || ((((uintptr_t)dst) & 15) == 0 && (bytes & 15u) == 0)) {
 #ifndef SWARM_EXP_NOSTORE   // experiment build: everything but the obs stream (what the compute side alone costs)
             if (lane == 0) {   // one TMA bulk store for the whole group
+#ifdef SWARM_EXP_NOHINT_ST
+              bulk_s2g_s(dst, stage_s, bytes);
+#else
               bulk_s2g_s_hint(dst, stage_s, bytes, pol_ef);
+#endif
               bulk_commit();
             }
 #endif
