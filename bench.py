@@ -109,6 +109,8 @@ class ClockSampler:
 def host_cores():
     """Cores this process may run on.  torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arms ignore it and use every
     core of the box (the N >= 2 reference arms ran on one thread)."""
+    if os.environ.get("SWARM_BENCH_CORES"):      # test knob (tests/test_bench_contract.py): a small worker pool for the slow arms
+        return max(1, int(os.environ["SWARM_BENCH_CORES"]))
     try:
         return len(os.sched_getaffinity(0))
     except Exception:
@@ -239,6 +241,39 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
+def run_trainer_reference(args, rank, kind, workload, metric, kw):
+    """--impl reference for the caller-row workloads: the UNMODIFIED reference loop (A2C/train.py::train() with models.Policy,
+    or the DQL_model/DQLearning.py loop) from baseline/_ref, one copy per host core (baseline/ref_trainers.py), rank 0 only.
+    A step is one outer iteration of train() on ONE env (the reference is batch-1) / one pass of the deep-Q loop; the step
+    count is capped so that the run stays within a few minutes."""
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps if args.steps != 1024 else 10, 12 if kind == "a2c" else 60))
+    warm = max(0, min(args.warmup, 2))
+    cmd = [sys.executable, os.path.join(REPO, "baseline", "ref_trainers.py"), kind, "--steps", str(steps), "--warmup", str(warm),
+           "--procs", str(host_cores()), "--rollout-steps", str(args.rollout_steps)]
+    env = dict(os.environ)
+    env.pop("OMP_NUM_THREADS", None)
+    try:
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, env=env)
+        r = json.loads(p.stdout.strip().splitlines()[-1])
+    except Exception as exc:
+        r = {"unavailable": f"reference trainer runner failed: {exc!r}"}
+    if "unavailable" in r:
+        print(json.dumps({"impl": "reference", "metric": metric, "config": {"workload": workload}, "unavailable": r["unavailable"]}))
+        return
+    sample = (f"{r['procs']} independent copies (one per host core) of the UNMODIFIED reference loop from baseline/_ref, batch 1 each, "
+              f"{r['grid']}x{r['grid']}, {r['n_drones']} drones, {steps} steps of {r['env_steps_per_step']} env-step(s), {r['wall_s']:.1f} s")
+    v = r["value"]
+    print(json.dumps({
+        "impl": "reference", "metric": metric, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
+        "ms_per_step": r["wall_s"] / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": workload, **kw, "total_envs": r["procs"], "rollout_steps": args.rollout_steps,
+                                         "note": "bounded sample: the reference loop is batch-1, so P = host cores envs, not the workload's 16 384"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": r["procs"], "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
 def teardown(dev, world, envs, comm=None, graphs=()):
     """Orderly exit (no os._exit: the interpreter's exit handlers must run so that the driver's hook sees which .so files
     this process mapped).  Order matters: captured graphs first (they reference the env buffers and, in --stats-mode nccl,
@@ -282,11 +317,7 @@ def run_a2c(args, rank, world, local):
     if args.envs:
         n_envs = args.envs
     if args.impl == "reference":
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "metric": "agent-steps/sec (env+policy, A2C train loop)", "config": {"workload": A2C_WORKLOAD},
-                              "unavailable": "the reference train() is pure Python/PyTorch under /root/reference and cannot travel to the GPU box; "
-                                             "measured in the build container: 47.2 agent-steps/s (8 cores, 10x10, 8 drones, MLP; BASELINE.md)"}))
-        return
+        return run_trainer_reference(args, rank, "a2c", A2C_WORKLOAD, "agent-steps/sec (env+policy, A2C train loop, device-timed)", kw)
     quiet_stdout()
     import torch
     import torch.distributed as dist
@@ -392,11 +423,7 @@ def run_dql(args, rank, world, local):
     if args.envs:
         n_envs = args.envs
     if args.impl == "reference":
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "metric": "agent-steps/sec (env+agent, deep-Q loop)", "config": {"workload": DQL_WORKLOAD},
-                              "unavailable": "the reference DQLearning.py is pure Python/PyTorch under /root/reference and cannot travel to the GPU box; "
-                                             "measured in the build container: 15.9 agent-steps/s (8 cores, 10x10, 8 drones; profiles/r1_dql_reference_cpu.json)"}))
-        return
+        return run_trainer_reference(args, rank, "dql", DQL_WORKLOAD, "agent-steps/sec (env+agent, deep-Q loop, device-timed)", kw)
     quiet_stdout()
     import torch
     import torch.distributed as dist

@@ -37,12 +37,21 @@ def test_reference_arm_line():
     assert e2e["value"] == d["value"] and e2e["h2d_bytes_per_step"] == 0 and e2e["d2h_bytes_per_step"] == 0
 
 
+@pytest.mark.timeout(900)
 @pytest.mark.parametrize("workload", ["cfg4_a2c", "cfg4_dql"])
-def test_caller_rows_reference_arm_says_unavailable(workload):
-    p = _run("--impl", "reference", "--workload", workload)
-    assert p.returncode == 0
+def test_caller_rows_reference_arm(workload):
+    """The caller-row workloads' reference arm runs the UNMODIFIED reference loop from baseline/_ref on the host cores (or says why
+    it cannot when the reference is not installed)."""
+    p = _run("--impl", "reference", "--workload", workload, "--steps", "1", "--warmup", "0", timeout=800,
+             env=dict(os.environ, SWARM_BENCH_CORES="2"))
+    assert p.returncode == 0, p.stderr[-2000:]
     d = json.loads(p.stdout.strip().splitlines()[-1])
-    assert d["impl"] == "reference" and "unavailable" in d and d["config"]["workload"] == workload
+    assert d["impl"] == "reference" and d["config"]["workload"] == workload
+    if os.path.exists(os.path.join(REPO, "baseline", "_ref", "A2C", "train.py")):
+        assert d["value"] > 0 and d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] == 2
+        assert "UNMODIFIED" in d["cpu_baseline"]["sample"] and d["e2e"]["value"] == d["value"]
+    else:
+        assert "unavailable" in d
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="only meaningful without a GPU")
