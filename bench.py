@@ -46,6 +46,17 @@ def algorithmic_bytes_per_env_step(kw, s_a=1, s_o=4):
     return D * s_a + 16 * D + 2 * D + D * WW + D * WW * s_o + 21
 
 
+def real_bytes_per_env_step(kw, s_a=1, s_o=4):
+    """DRAM bytes one env-step moves with the resident layout of DESIGN.md §3 (1 bit per cell, 32-byte anomaly list, float2
+    positions read + written, int4 meta read + written) — the layout-dependent counterpart of algorithmic_bytes_per_env_step."""
+    D, RC = kw["n_drones"], kw["row_count"] * kw["col_count"]
+    words = ((RC + 31) // 32 + 3) // 4 * 4
+    state = words * 4 + 32 + 16 * D + 32 + D * s_a + 5
+    if kw["obs_mode"] == "full":
+        return state + RC * s_o
+    return state + D * kw["window"] ** 2 * s_o
+
+
 def load_peak():
     path = os.path.join(REPO, "MEASURED_PEAKS.json")
     try:
@@ -745,6 +756,34 @@ def measure_rollout(torch, dist, dev, world, envs, acts, T, D, per, bytes_env, p
     return out
 
 
+def copy_same_bytes_us(torch, dev, nbytes, n=32, reps=8):
+    """A plain device copy that moves as many bytes (read + write) as one step of the workload really moves, under the same
+    conditions as `value`: CUDA graph of n copies over 4 rotating buffer pairs (> L2), back to back.  What the memory system
+    gives a launch of THIS size — the measured copy peak of MEASURED_PEAKS.json is for 4 GB copies, whose ramp and tail are
+    amortised away."""
+    half = max(1 << 20, int(nbytes) // 2 // 16 * 16)
+    src = [torch.empty(half, dtype=torch.uint8, device=dev) for _ in range(4)]
+    dst = [torch.empty(half, dtype=torch.uint8, device=dev) for _ in range(4)]
+    for i in range(4):
+        dst[i].copy_(src[i])
+    torch.cuda.synchronize(dev)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(n):
+            dst[i % 4].copy_(src[i % 4])
+    g.replay()
+    torch.cuda.synchronize(dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(reps):
+        g.replay()
+    t1.record()
+    torch.cuda.synchronize(dev)
+    us = t0.elapsed_time(t1) / (n * reps) * 1e3
+    g.reset()
+    return us, 2 * half
+
+
 def launch_floor_us(torch, dev, n=32, reps=20):
     """Step-to-step time of a CUDA graph of n dependent launches of a one-element kernel: what ANY one-launch-per-step loop
     pays per step on this box before doing work (context for the small workloads' roofline fractions)."""
@@ -992,6 +1031,8 @@ def main():
                                 ms_total / K if world == 1 else None, loop, rollout)
 
     floor_us = launch_floor_us(torch, dev)
+    moved = real_bytes_per_env_step(kw, s_o=s_o) * n_envs          # what the resident layout really moves per launch
+    copy_us, copy_bytes = copy_same_bytes_us(torch, dev, moved)
     # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region).
     # Headline format: uint8 observations (values 0 / 1 / U, pad 255) — the reference's obs are small integers (int64 on the
     # host, A2C/noVis_sim.py:168-170) that its callers cast to float32 themselves (A2C/train.py:21-24), so a byte per cell is
@@ -1067,6 +1108,10 @@ def main():
                                 "steps": E, "ms_per_step": ef_ms / E, "obs_format": "float32 (what the reference's callers cast to)",
                                 "d2h_gbs_per_rank": ef_d2h / (ef_ms / E * 1e-3) / 1e9},
             "rollout": rollout, "launch_floor_us": floor_us,
+            "same_size_copy": {"us": copy_us, "bytes": copy_bytes, "gbs": copy_bytes / (copy_us * 1e-6) / 1e9,
+                               "step_over_copy": (ms_total / K * 1e3) / copy_us,
+                               "what": "a plain torch device copy of as many bytes (read + write) as one step really moves with this layout, "
+                                       "graph-replayed like `value`: the memory system's answer for a launch of this size"},
             "strong_scaling": strong,
             "stats_check": stats_check, "stats_global_env_batch0": stats_global,
             "gpu_launches": launches, "clocks": dict(clocks, window=f"{hold * n_act} untimed steps + the {K} timed steps, continuous load"),

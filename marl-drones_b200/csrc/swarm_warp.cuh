@@ -262,9 +262,13 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
     }
     if (valid && tl == 0) m = meta_tma ? reinterpret_cast<const int4*>(in + p.off_meta)[wib * EPW + tile] : make_int4(0, 0, 0, 0);
 
+    int a_next = 0;   // rollout: the NEXT step's action is requested a whole step ahead, so its HBM latency is off the chain
     for (int t = 0; t < T; ++t, aidx += (size_t)N * D, ridx += N) {
-      if (t > 0 && active && (flags & F_MOVE))   // rollout: positions / meta are carried in registers, actions are re-read
-        a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
+      if (t > 0) a = a_next;   // rollout: positions / meta are carried in registers, actions are re-read
+      if (!LEAN && t + 1 < T && active && (flags & F_MOVE)) {
+        const size_t an = aidx + (size_t)N * D;
+        a_next = FAST ? (int)__ldg((const uint8_t*)io.actions + an) : load_action(io.actions, io.act_dtype, (long long)an);
+      }
 
       // ---- stage (1): action decode + move + clip (noVis_sim.py:117-135)
       if (active && (flags & F_MOVE)) {
