@@ -124,16 +124,10 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
   if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0 && threadIdx.x == 0)
     peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
   const int S = p.n_stages;
-  if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
-  if (threadIdx.x < MAX_STAGES) s_cnt[threadIdx.x] = 0;
-  if (threadIdx.x < 8)
-    s_dq[threadIdx.x] = make_float2(threadIdx.x == 1 ? p.ss : (threadIdx.x == 3 ? -p.ss : 0.f), threadIdx.x == 2 ? p.ss : (threadIdx.x == 0 ? -p.ss : 0.f));
-  build_window_tables<OT>(p, cvt, lut, MODE == 1 ? 256 : 16, WIN5 ? padx : nullptr, WIN5 ? pady : nullptr, threadIdx.x, blockDim.x);
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) mbar_init(&full_bar[s], 1);
+  if (threadIdx.x == 0) {   // the thread that initialises the barriers also issues the first S stage loads (below), BEFORE the
+    for (int s = 0; s < S; ++s) mbar_init(&full_bar[s], 1);   // CTA builds its tables: their HBM latency overlaps the prologue
     fence_mbar_init();
   }
-  __syncthreads();
   // CTA shared memory: [obs staging: wpb x stage_bytes][input stage 0] ... [input stage S-1][slack]
   OT* const stage = reinterpret_cast<OT*>(smem_raw + (size_t)wib * p.stage_bytes);   // this warp's [EPW][D][W*W] staging (WINDOW)
   unsigned char* const inbuf0 = smem_raw + (size_t)wpb * p.stage_bytes;
@@ -216,6 +210,12 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
   };
   if (threadIdx.x == 0)
     for (int k = 0; k < S; ++k) refill(k, k);
+  if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
+  if (threadIdx.x < MAX_STAGES) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x < 8)
+    s_dq[threadIdx.x] = make_float2(threadIdx.x == 1 ? p.ss : (threadIdx.x == 3 ? -p.ss : 0.f), threadIdx.x == 2 ? p.ss : (threadIdx.x == 0 ? -p.ss : 0.f));
+  build_window_tables<OT>(p, cvt, lut, MODE == 1 ? 256 : 16, WIN5 ? padx : nullptr, WIN5 ? pady : nullptr, threadIdx.x, blockDim.x);
+  __syncthreads();
 
   uint32_t par = 0u;   // parity of the current use of the stages (flips every S iterations)
   int s = 0;
