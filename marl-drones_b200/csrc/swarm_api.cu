@@ -30,6 +30,7 @@ struct SwarmEnv {
   float* h_rew_dev;
   uint8_t* h_done_dev;
   int* cover_dev;
+  uint32_t* tables_dev;   // DevParams::tables
   // peer-memory statistics exchange
   unsigned long long* mbox;          // this rank's mailbox, int64 [SWARM_MAX_RANKS][SWARM_MBOX_SLOT]
   unsigned long long* gstats_dev;    // int64[8] scratch for swarm_stats_global with a host destination
@@ -284,6 +285,7 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   if (p.list_mode) alloc((void**)&p.alist, N * 8 * sizeof(uint32_t));
   else alloc((void**)&p.anomp, N * p.env_words * sizeof(uint32_t));
   alloc((void**)&p.sched, 16);
+  alloc((void**)&e->tables_dev, 1536 * sizeof(uint32_t));
   alloc((void**)&p.pos, N * p.D * sizeof(float2));
   alloc((void**)&p.meta, N * sizeof(int4));
   if (p.has_wait) alloc((void**)&p.wait, N * RC * sizeof(int16_t));
@@ -299,6 +301,9 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   cudaMemsetAsync(p.sched, 0, 16, 0);
   cudaMemsetAsync(e->stats_dev, 0, 64, 0);
   cudaMemsetAsync(p.meta, 0, N * sizeof(int4), 0);
+  p.tables = e->tables_dev;
+  if (p.obs_dtype == SWARM_DTYPE_F32) build_tables_kernel<float><<<1, 256, 0, 0>>>(p, e->tables_dev);
+  else build_tables_kernel<uint8_t><<<1, 256, 0, 0>>>(p, e->tables_dev);
   reset_kernel<<<grid_blocks(e, p.N), 256, 0, 0>>>(p, nullptr, 0);
   e->launches++;
   err = cudaStreamSynchronize(0);
@@ -321,7 +326,7 @@ extern "C" int swarm_destroy(SwarmEnv* e) {
   if (cudaGetDevice(&cur) == cudaSuccess && cur != e->cfg.device) cudaSetDevice(e->cfg.device);
   cudaDeviceSynchronize();
   cudaFree(e->p.cov); cudaFree(e->p.anomp); cudaFree(e->p.alist); cudaFree(e->p.sched); cudaFree(e->p.pos); cudaFree(e->p.meta); cudaFree(e->p.wait); cudaFree(e->p.err);
-  cudaFree(e->stats_dev); cudaFree(e->cover_dev);
+  cudaFree(e->stats_dev); cudaFree(e->cover_dev); cudaFree(e->tables_dev);
   cudaFree(e->h_act_dev); cudaFree(e->h_obs_dev); cudaFree(e->h_rew_dev); cudaFree(e->h_done_dev);
   for (int r = 0; r < SWARM_MAX_RANKS; ++r)
     if (e->peer_open[r]) cudaIpcCloseMemHandle(e->peer_open[r]);

@@ -73,6 +73,7 @@ struct DevParams {
   uint32_t* anomp;    // anomaly bit plane (PLANE mode) or null
   uint32_t* alist;    // anomaly list (LIST mode) or null
   int* sched;         // int[4] dynamic CTA-group scheduler of the staged kernel: {next group, CTAs done, -, -}
+  const uint32_t* tables;   // W == 5 window tables built once per handle (build_tables_kernel): [lut 1024 words][padx 256][pady 256]
   float2* pos;
   int4* meta;
   int16_t* wait;

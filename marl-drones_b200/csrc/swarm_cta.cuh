@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   // W == 5 window fast path (LIST mode, wide path): the tables of swarm_window.cuh, and a staging image of the env's
   // [D][25] obs block behind the plane in dynamic shared memory, streamed out with ONE TMA bulk store per env
   __shared__ __align__(16) uint32_t lut[256 * (sizeof(OT) == 4 ? 4 : 1)];
-  __shared__ uint32_t padx[256], pady[256];
+  __shared__ __align__(16) uint32_t padx[256], pady[256];
   CtaView v;
   v.sc = staged ? reinterpret_cast<uint32_t*>(cta_smem) : nullptr;
   v.sa = (staged && !p.list_mode) ? reinterpret_cast<const uint32_t*>(cta_smem) + p.env_words : nullptr;
@@ -264,8 +264,14 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   uint32_t phase = 0;
   StatAcc acc;
   const uint32_t plane_bytes = (uint32_t)p.env_words * 4u;
-  auto load_view = [&](int env) {   // one thread: the env's plane(s) / list by TMA
-    mbar_expect_tx(&bar, p.list_mode ? plane_bytes + 32u : 2u * plane_bytes);
+  constexpr uint32_t lut_bytes = 256u * (sizeof(OT) == 4 ? 16u : 4u);
+  auto load_view = [&](int env, bool with_tables = false) {   // one thread: the env's plane(s) / list (+ the window tables) by TMA
+    mbar_expect_tx(&bar, (p.list_mode ? plane_bytes + 32u : 2u * plane_bytes) + (with_tables ? lut_bytes + 2048u : 0u));
+    if (with_tables) {
+      bulk_g2s(lut, p.tables, lut_bytes, &bar);
+      bulk_g2s(padx, p.tables + 1024, 1024u, &bar);
+      bulk_g2s(pady, p.tables + 1280, 1024u, &bar);
+    }
     bulk_g2s(v.sc, p.cov + (size_t)env * p.env_words, plane_bytes, &bar);
     if (p.list_mode) bulk_g2s(s_list, p.alist + (size_t)env * 8, 32u, &bar);
     else bulk_g2s(const_cast<uint32_t*>(v.sa), p.anomp + (size_t)env * p.env_words, plane_bytes, &bar);
@@ -276,15 +282,11 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   const uint32_t win_bytes = (uint32_t)p.D * 25u * (uint32_t)sizeof(OT);
   const bool win5 = wide && want_obs && p.list_mode && p.obs_mode == 1 && p.W == 5 && (win_bytes & 15u) == 0u && staged == 2;
   OT* const s_win = reinterpret_cast<OT*>(cta_smem + (((size_t)p.env_words * 4 + 15) & ~(size_t)15));   // staged == 2: room behind the plane
-  if (win5) {
-    const ObsCvt<OT> cvt(p);
-    build_window_tables<OT>(p, cvt, lut, 256, padx, pady, threadIdx.x, blockDim.x);
-    __syncthreads();
-  }
+
   for (int env = blockIdx.x; env < p.N; env += gridDim.x) {
     int4 m_pre = make_int4(0, 0, 0, 0);
     if (staged && threadIdx.x == 0) {
-      load_view(env);
+      load_view(env, win5 && env == (int)blockIdx.x);   // the CTA's first env brings the window tables along
       if (wide) m_pre = __ldcg(p.meta + env);   // in flight together with the planes and the positions
     }
     bool landed = !staged;
@@ -355,15 +357,12 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   }
 
   if (win5 && threadIdx.x == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
-  if (io.stats && (flags & F_REWARD)) {   // only warp 0 accumulated
-    if (warp == 0) {
-      long long vv[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
+  if (io.stats && (flags & F_REWARD)) {   // only lane 0 of warp 0 accumulated (step_env_warp): no reduction needed
+    if (threadIdx.x == 0) {
+      const long long vv[6] = {acc.rew, (long long)acc.done, acc.len, acc.ret, (long long)acc.cells, (long long)acc.anom};
 #pragma unroll
-      for (int k = 0; k < 6; ++k) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) vv[k] += __shfl_xor_sync(FULL, vv[k], o);
-        if (lane == 0 && vv[k] != 0) atomicAdd(io.stats + 2 + k, (unsigned long long)vv[k]);
-      }
+      for (int k = 0; k < 6; ++k)
+        if (vv[k] != 0) atomicAdd(io.stats + 2 + k, (unsigned long long)vv[k]);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
       atomicAdd(io.stats + 0, (unsigned long long)((long long)p.N * io.T));

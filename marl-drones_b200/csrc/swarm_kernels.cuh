@@ -113,6 +113,14 @@ __global__ void __launch_bounds__(256) get_state_kernel(const __grid_constant__ 
   }
 }
 
+// The W == 5 window tables of swarm_window.cuh, built once per handle into DevParams::tables (the CTA kernel brings them on
+// chip with three bulk copies instead of recomputing them in each of its one-env CTAs).
+template <typename OT>
+__global__ void __launch_bounds__(256) build_tables_kernel(const __grid_constant__ DevParams p, uint32_t* tab) {
+  const ObsCvt<OT> cvt(p);
+  build_window_tables<OT>(p, cvt, tab, 256, tab + 1024, tab + 1280, threadIdx.x, blockDim.x);
+}
+
 // K1 as a standalone stage: one thread per (env, drone).
 __global__ void __launch_bounds__(256) move_kernel(const __grid_constant__ DevParams p, const void* actions, int act_dtype) {
   const long long n = (long long)p.N * p.D;
