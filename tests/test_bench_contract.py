@@ -88,3 +88,21 @@ def test_timed_region_is_graph_replay_at_any_step_count():
     assert FakeLoop().describe(20, None).startswith("eager")
     src = open(os.path.join(REPO, "bench.py")).read()
     assert "os._exit" not in src.replace("no os._exit", "")
+
+
+def test_byte_accounting_of_the_bench_line():
+    """SURVEY §8(d) canonical bytes (the roofline numerator) and the bytes the round-2 layout really moves."""
+    sys.path.insert(0, REPO)
+    import bench
+    kw3 = bench.WORKLOADS["cfg3"][1]
+    assert bench.algorithmic_bytes_per_env_step(kw3) == 2325                      # 145.3 B per agent-step
+    assert bench.real_bytes_per_env_step(kw3) == 512 + 32 + 256 + 32 + 16 + 5 + 1600   # plane, list, pos r+w, meta r+w, actions, reward+done, obs
+    assert round(bench.real_bytes_per_env_step(kw3) * 65536 / 1e6, 1) == 160.8
+    assert bench.algorithmic_bytes_per_env_step(bench.WORKLOADS["cfg2"][1]) == 5213
+    assert bench.algorithmic_bytes_per_env_step(bench.WORKLOADS["cfg4"][1]) == 665
+    assert bench.algorithmic_bytes_per_env_step(bench.WORKLOADS["cfg5a"][1]) == 328853
+    for w in ("cfg2", "cfg4", "cfg5a"):                                           # 1 bit per cell: less than the canon's byte per cell
+        kw = bench.WORKLOADS[w][1]
+        assert bench.real_bytes_per_env_step(kw) <= bench.algorithmic_bytes_per_env_step(kw)
+    kw = bench.WORKLOADS["cfg5b"][1]                                              # the whole 8 KiB plane is staged to serve 64 windows
+    assert bench.real_bytes_per_env_step(kw) == 8192 + 32 + 1024 + 32 + 64 + 5 + 6400
