@@ -959,12 +959,3 @@ extern "C" int swarm_stats_global_host(SwarmEnv* e, int64_t min_pushes, int64_t*
     if (out_host[k] != -1) return SWARM_OK;
   return SWARM_ERR_TIMEOUT;   // every entry -1: the reduce kernel gave up (it never sums a torn slot)
 }
-
-#if SWARM_TRACE   // instrumented builds only (nvcc -DSWARM_TRACE=1, tools/trace.py); not part of include/swarm_b200.h
-extern "C" int swarm_debug_cta(unsigned long long* out) {
-  return cudaMemcpyFromSymbol(out, swarm::g_cta_t, sizeof(unsigned long long) * 4096) == cudaSuccess ? 0 : -3;
-}
-extern "C" int swarm_debug_trace(unsigned long long* out) {
-  return cudaMemcpyFromSymbol(out, swarm::g_trace, sizeof(unsigned long long) * 16 * 8 * 8) == cudaSuccess ? 0 : -3;
-}
-#endif
