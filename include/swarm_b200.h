@@ -162,6 +162,19 @@ int swarm_rollout(SwarmEnv* env, int32_t T, const uint8_t* actions, void* obs_ou
 int swarm_step_host(SwarmEnv* env, const uint8_t* actions_host, void* obs_host,
                     float* reward_host, uint8_t* done_host, int64_t* stats_host, void* stream);
 
+/* swarm_step_host without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code next to CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, results and synchronisation as swarm_step_host, but the device-side staging of actions / obs / reward /
+ * done / statistics lives in ONE file-scope `static __device__` array of SWARM_STATIC_SCRATCH_BYTES that every GPU which
+ * loads the library holds until the process exits; the call issues no cudaMalloc / cudaFree (swarm_create did the handle's).
+ * Limit: 256 + up256(N*D) + up256(4*N) + up256(N) + up256(obs bytes, 0 when obs_host == NULL) <= SWARM_STATIC_SCRATCH_BYTES,
+ * else SWARM_ERR_INVALID_ARG with the sizes spelled out in swarm_last_cuda_error().  The array is shared by every handle and
+ * stream of the process on that device and keeps the last call's contents (the statistics slot is cleared per call): two
+ * calls that overlap on the GPU race — serialise them. */
+#define SWARM_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int swarm_step_host_static(SwarmEnv* env, const uint8_t* actions_host, void* obs_host,
+                           float* reward_host, uint8_t* done_host, int64_t* stats_host, void* stream);
+
 /* -- per-stage entry points (unit parity of the four stages named in the north star) --------- */
 /* K1 action decode + move + clip (A2C/noVis_sim.py:117-135): updates resident positions. */
 int swarm_stage_move(SwarmEnv* env, const void* actions, int action_dtype, void* stream);

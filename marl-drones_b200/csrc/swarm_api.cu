@@ -959,3 +959,59 @@ extern "C" int swarm_stats_global_host(SwarmEnv* e, int64_t min_pushes, int64_t*
     if (out_host[k] != -1) return SWARM_OK;
   return SWARM_ERR_TIMEOUT;   // every entry -1: the reduce kernel gave up (it never sums a torn slot)
 }
+
+// ------------------------------------------------------------------------------------------------ allocation-free host step
+// swarm_step_host stages its host buffers through device memory it cudaMalloc's on first use.  Callers that may not allocate
+// (CUDA-graph-adjacent serving loops, harnesses that forbid cudaMalloc) get the same call with the staging in this file-scope
+// array instead: SWARM_STATIC_SCRATCH_BYTES on every device that loads the library, held until the process exits.  In host
+// code `g_static_scratch` is only a stand-in for the symbol — the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.  Every call (any handle, any stream) shares the array: calls that overlap on the GPU race.
+static __device__ __align__(256) unsigned char g_static_scratch[SWARM_STATIC_SCRATCH_BYTES];
+
+static int static_scratch_ptr(int device, unsigned char** out) {
+  static unsigned char* ptr_of[64] = {nullptr};   // per device ordinal; resolved with that device current (use_device ran)
+  if (device < 0 || device >= 64) return SWARM_ERR_INVALID_ARG;
+  if (!ptr_of[device]) {
+    unsigned char* ptr = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress((void**)&ptr, g_static_scratch));
+    if (!ptr) return SWARM_ERR_CUDA;
+    ptr_of[device] = ptr;
+  }
+  *out = ptr_of[device];
+  return SWARM_OK;
+}
+
+extern "C" int swarm_step_host_static(SwarmEnv* e, const uint8_t* actions_host, void* obs_host, float* reward_host,
+                                      uint8_t* done_host, int64_t* stats_host, void* stream) {
+  if (!e || !actions_host || !reward_host || !done_host) return SWARM_ERR_INVALID_ARG;
+  const size_t N = (size_t)e->p.N, nact = N * e->p.D, nobs = obs_host ? (size_t)swarm_obs_bytes(e) : 0;
+  auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+  // layout: statistics int64[8] | actions uint8[N][D] | reward float[N] | done uint8[N] | obs   (each 256 B aligned)
+  const size_t o_stats = 0, o_act = 256, o_rew = o_act + up(nact), o_done = o_rew + up(N * sizeof(float)),
+               o_obs = o_done + up(N), need = o_obs + up(nobs);
+  if (need > (size_t)SWARM_STATIC_SCRATCH_BYTES) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err),
+             "swarm_step_host_static: staging for %zu envs needs %zu bytes, the static scratch holds %d (use swarm_step_host)",
+             N, need, (int)SWARM_STATIC_SCRATCH_BYTES);
+    return SWARM_ERR_INVALID_ARG;
+  }
+  int rc = use_device(e);
+  if (rc) return rc;
+  unsigned char* s = nullptr;
+  if ((rc = static_scratch_ptr(e->cfg.device, &s)) != SWARM_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemcpyAsync(s + o_act, actions_host, nact, cudaMemcpyHostToDevice, st));
+  // the array keeps the previous call's contents; only the statistics accumulate, so only they start from zero
+  if (stats_host) CUDA_TRY(cudaMemsetAsync(s + o_stats, 0, 64, st));
+  StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
+  io.actions = s + o_act; io.act_dtype = SWARM_ACT_U8; io.obs_out = obs_host ? (void*)(s + o_obs) : nullptr;
+  io.reward_out = (float*)(s + o_rew); io.done_out = s + o_done; io.stats = stats_host ? (unsigned long long*)(s + o_stats) : nullptr;
+  rc = launch_step(e, io, st);
+  if (rc) return rc;
+  if (obs_host) CUDA_TRY(cudaMemcpyAsync(obs_host, s + o_obs, nobs, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(reward_host, s + o_rew, N * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(done_host, s + o_done, N, cudaMemcpyDeviceToHost, st));
+  if (stats_host) CUDA_TRY(cudaMemcpyAsync(stats_host, s + o_stats, 64, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return SWARM_OK;
+}

@@ -143,6 +143,22 @@ class BatchedDroneEnv:
         check(self._L.swarm_step_host(self._h, hp(actions_host), hp(obs_host), hp(reward_host), hp(done_host),
                                       hp(stats_host), self._stream()))
 
+    def step_host_static(self, actions_host, obs_host, reward_host, done_host, stats_host=None):
+        """step_host through swarm_step_host_static: the device-side staging is the library's fixed static array
+        (SWARM_STATIC_SCRATCH_BYTES), so the call allocates nothing; sizes beyond it raise SwarmError.  No counterpart in
+        the reference (added for callers that cannot call cudaMalloc); calls that overlap on the GPU race."""
+        def hp(a):
+            if a is None:
+                return None
+            return C.c_void_p(a.data_ptr() if torch.is_tensor(a) else a.ctypes.data)
+        rc = self._L.swarm_step_host_static(self._h, hp(actions_host), hp(obs_host), hp(reward_host), hp(done_host),
+                                            hp(stats_host), self._stream())
+        if rc == -1:
+            msg = self._L.swarm_last_cuda_error().decode()
+            if "static scratch" in msg:
+                raise SwarmError(f"swarm_b200 error -1: {msg}")
+        check(rc)
+
     def close(self, collective=True):
         """Destroys the handle.  With peer statistics enabled across ranks (enable_peer_stats on a process group) the close is
         COLLECTIVE: every rank stops pushing and unmaps its peers' mailboxes, then all ranks meet at a barrier, and only then
