@@ -365,6 +365,35 @@ extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* 
 }
 
 // ------------------------------------------------------------------------------------------------ launches
+// Step launches are programmatic dependent launches (cudaLaunchAttributeProgrammaticStreamSerialization): the kernels call
+// griddepcontrol.launch_dependents when their main loop is done and griddepcontrol.wait before their first global access, so
+// the launch latency, CTA start-up and shared-memory prologue of step k+1 overlap the epilogue and drain of whatever kernel
+// precedes it on the stream (under stream capture the edge becomes a programmatic graph dependency).  Measured per shape in
+// DESIGN.md §5 (triggering at the kernel's TOP instead lets waiting CTAs crowd the running grid and loses).
+// SWARM_PDL=0 launches plain kernels (A/B measurements).
+static bool pdl_enabled() {
+  static const bool on = [] {
+    const char* s = getenv("SWARM_PDL");
+    return !(s && s[0] == '0');
+  }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_step_kernel(void (*kernel)(KArgs...), int blocks, int threads, int smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)blocks);
+  cfg.blockDim = dim3((unsigned)threads);
+  cfg.dynamicSmemBytes = (size_t)smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // One instantiation of the staged kernel: raises its dynamic shared-memory limit once per handle, sizes the persistent
 // grid from the occupancy calculator (resident CTAs only) and launches.
 template <int TS, typename OT, int MODE, int WC, bool FAST, bool LEAN = false>
@@ -388,8 +417,7 @@ static cudaError_t launch_warp_inst(SwarmEnv* e, const StepIO& io, cudaStream_t 
     resident = (per_sm > 0 ? per_sm : 1) * e->sm_count;
   }
   const long long blocks = blocks_needed < resident ? blocks_needed : resident;
-  kernel<<<(int)blocks, e->wpb * 32, smem, st>>>(e->p, io);
-  return cudaSuccess;
+  return launch_step_kernel(kernel, (int)blocks, e->wpb * 32, smem, st, e->p, io);
 }
 
 template <int TS, typename OT>
@@ -459,7 +487,7 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io_in, cudaStream_t
     }
     long long blocks = p.N;
     if (blocks > e->resident[0]) blocks = e->resident[0];   // resident CTAs only, grid-stride beyond
-    step_cta_kernel<OT><<<(int)blocks, threads, smem, st>>>(p, io, staged);
+    err = launch_step_kernel(step_cta_kernel<OT>, (int)blocks, threads, smem, st, p, io, staged);
   }
   e->launches++;
   return err;

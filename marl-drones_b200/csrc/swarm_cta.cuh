@@ -254,12 +254,13 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   const int flags = io.flags;
   const bool want_obs = (flags & F_OBS) && io.obs_out != nullptr;
   const bool stepping = (flags & (F_MOVE | F_SCATTER | F_REWARD)) != 0;
-  if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0 && threadIdx.x == 0)
-    peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
   if (staged && threadIdx.x == 0) {
     mbar_init(&bar, 1);
     fence_mbar_init();
   }
+  pdl_wait();
+  if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0 && threadIdx.x == 0)
+    peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
   __syncthreads();
   uint32_t phase = 0;
   StatAcc acc;
@@ -356,6 +357,7 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
     }
   }
 
+  pdl_launch_dependents();   // main loop done: the next launch on the stream may bring its CTAs in (they run their prologue, then pdl_wait)
   if (win5 && threadIdx.x == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
   if (io.stats && (flags & F_REWARD)) {   // only lane 0 of warp 0 accumulated (step_env_warp): no reduction needed
     if (threadIdx.x == 0) {

@@ -121,8 +121,6 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
   const bool has_wait = FAST ? false : (p.has_wait != 0);
   const bool want_stats = LEAN ? true : (io.stats != nullptr && (flags & F_REWARD));
   const ObsCvt<OT> cvt(p);
-  if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0 && threadIdx.x == 0)
-    peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
   const int S = p.n_stages;
   if (threadIdx.x == 0) {   // the thread that initialises the barriers also issues the first S stage loads (below), BEFORE the
     for (int s = 0; s < S; ++s) mbar_init(&full_bar[s], 1);   // CTA builds its tables: their HBM latency overlaps the prologue
@@ -208,13 +206,18 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
     }
     issue(cg, s);
   };
-  if (threadIdx.x == 0)
+  if (threadIdx.x == 0) {
+    pdl_wait();   // everything above touched only shared memory and kernel parameters; from here on we read what earlier launches wrote
+    if (p.peers.n_ranks > 0 && (io.flags & F_PUSH) && io.stats && blockIdx.x == 0)
+      peer_stats_push(p.peers, io.stats);   // multi-GPU: publish the totals of the launches before this one (see PeerStats)
     for (int k = 0; k < S; ++k) refill(k, k);
+  }
   if (threadIdx.x < 6) s_stats[threadIdx.x] = 0ull;
   if (threadIdx.x < MAX_STAGES) s_cnt[threadIdx.x] = 0;
   if (threadIdx.x < 8)
     s_dq[threadIdx.x] = make_float2(threadIdx.x == 1 ? p.ss : (threadIdx.x == 3 ? -p.ss : 0.f), threadIdx.x == 2 ? p.ss : (threadIdx.x == 0 ? -p.ss : 0.f));
   build_window_tables<OT>(p, cvt, lut, MODE == 1 ? 256 : 16, WIN5 ? padx : nullptr, WIN5 ? pady : nullptr, threadIdx.x, blockDim.x);
+  pdl_wait();   // every thread, before its own global accesses (thread 0 has passed it already)
   __syncthreads();
 
   uint32_t par = 0u;   // parity of the current use of the stages (flips every S iterations)
@@ -464,6 +467,7 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
     }
     if (++s == S) { s = 0; par ^= 1u; }
   }
+  pdl_launch_dependents();   // main loop done: the next launch on the stream may bring its CTAs in (they run their prologue, then pdl_wait)
   if (lane == 0) bulk_wait_read0();   // shared memory must outlive the last bulk store's reads
 
   if (want_stats) {   // one lane per warp adds the warp's (uniform) totals; zero entries are skipped
