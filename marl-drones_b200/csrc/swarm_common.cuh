@@ -95,7 +95,6 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-// orders this thread's earlier generic-proxy shared-memory accesses before later async-proxy (TMA) ones
 // Programmatic dependent launch (sm_90+): a step launch carries cudaLaunchAttributeProgrammaticStreamSerialization.  Once every
 // CTA of the launch before it has called `pdl_launch_dependents` (after its main loop), its own CTAs may become resident and run
 // their prologue (barrier init, table build); `pdl_wait` then returns once every prerequisite grid has completed and its memory
@@ -103,6 +102,7 @@ __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier
 // without the attribute.
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// orders this thread's earlier generic-proxy shared-memory accesses before later async-proxy (TMA) ones
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");

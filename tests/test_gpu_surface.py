@@ -110,6 +110,37 @@ def test_step_host_matches_device_step():
     g1.close()
 
 
+@pytest.mark.parametrize("name,N", [("cfg3", 4100), ("cfg1", 16389), ("cfg5b", 700), ("cfg2", 1500)])
+def test_step_host_large_obs_matches_device_step(name, N):
+    """swarm_step_host with observations of 4 MiB and more (ragged env counts, both kernels) against swarm_step on a twin handle.
+    (Written for an env-chunked, copy-overlapped form of swarm_step_host that measured no faster and was dropped)"""
+    from swarm_b200 import BatchedDroneEnv
+    kw = dict(SHAPES[name])
+    D = kw["n_drones"]
+    host = BatchedDroneEnv(N, auto_reset=True, seed=21, **kw)
+    dev = BatchedDroneEnv(N, auto_reset=True, seed=21, **kw)
+    assert int(np.prod(host.obs_shape)) * 4 >= 4 << 20
+    a_h = torch.empty((N, D), dtype=torch.uint8).pin_memory()
+    obs_h = torch.empty(host.obs_shape, dtype=torch.float32).pin_memory()
+    rew_h = torch.empty(N, dtype=torch.float32).pin_memory()
+    done_h = torch.empty(N, dtype=torch.uint8).pin_memory()
+    stats_h = torch.zeros(8, dtype=torch.int64).pin_memory()
+    rs = np.random.RandomState(2)
+    total = torch.zeros(8, dtype=torch.int64)
+    for k in range(12):
+        a_h.copy_(torch.from_numpy(rs.randint(0, 4, (N, D)).astype(np.uint8)))
+        obs_h.fill_(-7)
+        host.step_host(a_h, obs_h, rew_h, done_h, stats_h)
+        obs, rew, done, _ = dev.step(a_h.cuda())
+        assert torch.equal(obs_h, obs.cpu()), k
+        assert torch.equal(rew_h, rew.cpu()) and torch.equal(done_h, done.cpu()), k
+        total += stats_h
+    assert torch.equal(total, dev.stats.cpu())
+    for x, y in zip(host.get_state(), dev.get_state()):
+        assert (x is None and y is None) or torch.equal(x, y)
+    host.close(); dev.close()
+
+
 def test_greedy_actions_match_oracle_and_finish_episodes():
     g, o = make_pair(33, auto_reset=False, seed=6, row_count=9, col_count=7, n_drones=3, step_size=1.0)
     for k in range(80):
