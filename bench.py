@@ -882,6 +882,10 @@ def main():
                     help="N > 1: how the per-step episode statistics cross GPUs — 'peer': pushed by the step kernel into "
                          "every rank's mailbox over NVLink peer memory (no collective kernel); 'nccl': swarm_stats_allreduce on a side stream")
     ap.add_argument("--stats-every", type=int, default=1, help="N > 1: all-reduce the episode statistics every K steps (0 = never)")
+    ap.add_argument("--dwell", action="store_true",
+                    help="dwell goals of SURVEY App. B.2 (swarmsim-2d/run_env.py:46-47): a cell is mapped only after 10 (normal) / 35 "
+                         "(anomalous) drone-ticks on it; the second run SURVEY §8(d) asks of cfg5.  The CPU baselines beside it stay "
+                         "the noVis env, which has no dwell")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
@@ -891,6 +895,8 @@ def main():
         return run_dql(args, rank, world, local)
     n_envs, kw = WORKLOADS[args.workload]
     kw = dict(kw)
+    if args.dwell:
+        kw.update(dwell_normal=10, dwell_anom=35)
     workload_envs = n_envs
     if args.envs:
         n_envs = args.envs
