@@ -197,6 +197,38 @@ __device__ __forceinline__ void scatter_drone(const DevParams& p, const CtaView&
   }
 }
 
+// Stage (2) with dwell goals (App. B.2) on the all-thread path: `s_cell[j]` holds drone j's candidate cell of this tick (-1: none).
+// The drones on one cell form a group; its lowest-indexed drone acts for all k of them, which is what processing them in index
+// order amounts to: the counter absorbs k ticks, or runs out — then the next drone in line maps the cell and the rest find it mapped.
+__device__ __forceinline__ int drone_candidate_cell(const DevParams& p, float2 q) {
+  const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f);
+  const double dx = (double)cx - (double)q.x, dy = (double)cy - (double)q.y;
+  return (dx * dx + dy * dy < p.cd2_thr) ? cy * p.R + cx : -1;
+}
+__device__ __forceinline__ void scatter_drone_dwell(const DevParams& p, const CtaView& v, int env, int d, const int* s_cell, int* s_pk) {
+  const int cell = s_cell[d];
+  if (cell < 0) return;
+  const uint32_t bit = 1u << (cell & 31);
+  if (!(v.sc[cell >> 5] & bit)) return;   // mapped before this tick (bits of OTHER cells of the word may be cleared meanwhile)
+  int k = 0;
+  bool leader = true;
+  for (int j = 0; j < p.D; ++j) {
+    const bool same = s_cell[j] == cell;
+    k += same ? 1 : 0;
+    leader = leader && !(same && j < d);
+  }
+  if (!leader) return;
+  int16_t* w = p.wait + (size_t)env * p.RC + cell;
+  const int wv = *w;
+  if (wv >= k) { *w = (int16_t)(wv - k); return; }
+  if (wv > 0) *w = 0;
+  atomicAnd(v.sc + (cell >> 5), ~bit);
+  atomicAnd(p.cov + (size_t)env * p.env_words + (cell >> 5), ~bit);   // write-through to HBM
+  const int cy = cell / p.R, cx = cell - cy * p.R;
+  const int an = cta_is_anomalous(p, v, env, cell, cx, cy) ? 1 : 0;
+  atomicAdd(s_pk, (10 + 20 * an) | (1 << 16) | (an << 24));
+}
+
 // CTA-wide stage (4) from the shared-memory view.  FULL: bits -> elements with 128-bit stores (+ the LIST patch after a
 // CTA barrier); WINDOW: one item = one window row of one drone.
 template <typename OT>
@@ -242,6 +274,7 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
   __shared__ int s_pk, s_reset;
   __shared__ __align__(16) uint32_t s_list[8];
   __shared__ float2 s_pos[256];   // this step's positions of the env (wide path): spread test and window emission read them here
+  __shared__ int s_cell[256];     // dwell goals on the wide path: each drone's candidate cell of this tick (-1: none)
   // W == 5 window fast path (LIST mode, wide path): the tables of swarm_window.cuh, and a staging image of the env's
   // [D][25] obs block behind the plane in dynamic shared memory, streamed out with ONE TMA bulk store per env
   __shared__ __align__(16) uint32_t lut[256 * (sizeof(OT) == 4 ? 4 : 1)];
@@ -278,7 +311,7 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
     else bulk_g2s(const_cast<uint32_t*>(v.sa), p.anomp + (size_t)env * p.env_words, plane_bytes, &bar);
   };
   // production path: stages (1)-(2) on all threads, one drone per thread (30 * 255 < 2^16 keeps the packed totals exact)
-  const bool wide = staged && (flags & (F_MOVE | F_SCATTER | F_REWARD)) == (F_MOVE | F_SCATTER | F_REWARD) && p.cd_fast && !p.has_wait &&
+  const bool wide = staged && (flags & (F_MOVE | F_SCATTER | F_REWARD)) == (F_MOVE | F_SCATTER | F_REWARD) && p.cd_fast &&
                     p.D <= 255 && p.D <= (int)blockDim.x;
   const uint32_t win_bytes = (uint32_t)p.D * 25u * (uint32_t)sizeof(OT);
   const bool win5 = wide && want_obs && p.list_mode && p.obs_mode == 1 && p.W == 5 && (win_bytes & 15u) == 0u && staged == 2;
@@ -301,10 +334,14 @@ __global__ void __launch_bounds__(256) step_cta_kernel(const __grid_constant__ D
         if (mine) {
           q = move_drone(p, io, t, env, threadIdx.x);
           s_pos[threadIdx.x] = q;
+          if (p.has_wait) s_cell[threadIdx.x] = drone_candidate_cell(p, q);
         }
         if (!landed) { mbar_wait(&bar, phase); phase ^= 1u; landed = true; }
         __syncthreads();   // s_pk is zero, the planes have landed
-        if (mine) scatter_drone(p, v, env, q, &s_pk);
+        if (mine) {
+          if (p.has_wait) scatter_drone_dwell(p, v, env, threadIdx.x, s_cell, &s_pk);
+          else scatter_drone(p, v, env, q, &s_pk);
+        }
         __syncthreads();   // clears (shared memory), positions (s_pos) and totals are visible to warp 0
         if (warp == 0 && step_env_warp(p, io, t, env, lane, acc, v, &s_pk, s_pos, t == 0 ? &m_pre : nullptr) && lane == 0) s_reset = 1;
         __syncthreads();   // warp 0's updates (auto-reset) are visible to the CTA

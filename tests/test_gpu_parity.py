@@ -144,6 +144,11 @@ def test_lockstep_edge_shapes(kw, auto_reset):
     dict(row_count=5, col_count=5, n_drones=12, step_size=1.0, dwell=(10, 35)),
     dict(row_count=8, col_count=8, n_drones=40, step_size=0.5, dwell=(2, 5)),
     dict(row_count=6, col_count=6, n_drones=4, step_size=1.0, dwell=(2, 3), collision_dist=1.2),
+    # the CTA kernel's all-thread path with dwell: groups of drones on one cell that span several warps, and the W = 5 window path
+    dict(row_count=3, col_count=3, n_drones=64, step_size=1.0, dwell=(10, 35)),
+    dict(row_count=4, col_count=5, n_drones=100, step_size=1.0, dwell=(7, 20), n_anamolous=3),
+    dict(row_count=40, col_count=40, n_drones=48, step_size=1.0, obs_mode=1, window=5, dwell=(2, 5)),
+    dict(row_count=12, col_count=9, n_drones=33, step_size=1.0, obs_mode=1, window=3, dwell=(1, 2), n_anamolous=12),
 ])
 def test_lockstep_dwell(kw):
     """Dwell counters (swarmsim-2d/goals.py semantics; ours, parity unpinned vs the reference)."""
