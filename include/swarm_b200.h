@@ -16,6 +16,10 @@
  *    DEVICE pointers on the handle's device and all work is enqueued asynchronously on
  *    the `stream` argument (a `cudaStream_t` passed as `void*`; NULL = legacy default stream).
  *    No hidden synchronisation: every device entry point is CUDA-graph capturable.
+ *    Step launches (swarm_step / swarm_rollout / swarm_stage_* / swarm_step_host*) are programmatic dependent launches: their
+ *    kernels start their shared-memory prologue while the kernel before them on the stream drains and wait (griddepcontrol.wait)
+ *    before touching global memory.  Nothing changes for the caller: work enqueued after them keeps its full stream-order
+ *    dependency (unless it opts into programmatic launch itself).  SWARM_PDL=0 in the environment launches them as plain kernels.
  *  - invalid actions do not trap; they set a sticky device error word that
  *    `swarm_device_error` reads (the Python facade turns it into the reference's
  *    AssertionError, A2C/noVis_sim.py:118-120).
