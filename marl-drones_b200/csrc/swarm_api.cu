@@ -423,11 +423,11 @@ static cudaError_t launch_warp_inst(SwarmEnv* e, const StepIO& io, cudaStream_t 
 template <int TS, typename OT>
 static cudaError_t launch_warp_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks, int smem) {
   const DevParams& p = e->p;
-  // FAST: every stage in one pass, uint8 actions, cd <= 0.5, no dwell — the swarm_step / swarm_rollout production path
-  const bool fast = (io.flags & F_ALL) == F_ALL && io.act_dtype == SWARM_ACT_U8 && p.cd_fast && !p.has_wait && p.f32_exact;
+  // FAST: every stage in one pass, cd <= 0.5, no dwell — the swarm_step / swarm_rollout production path (any action dtype)
+  const bool fast = (io.flags & F_ALL) == F_ALL && p.cd_fast && !p.has_wait && p.f32_exact && (io.act_dtype == SWARM_ACT_U8 || io.T == 1);
   // LEAN: the FAST kernel with the tail / rollout / alignment bookkeeping folded away (see step_warp_kernel)
   const int epw = 32 / TS;
-  const bool lean = fast && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epw == 0 && (epw * TS) % 16 == 0 &&
+  const bool lean = fast && io.act_dtype == SWARM_ACT_U8 && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epw == 0 && (epw * TS) % 16 == 0 &&
                     ((((uintptr_t)io.actions) | ((uintptr_t)io.obs_out)) & 15) == 0 && !getenv("SWARM_NO_LEAN");
   if (p.obs_mode == SWARM_OBS_FULL) {
     if (lean) return launch_warp_inst<TS, OT, 0, 0, true, true>(e, io, st, blocks, smem);

@@ -35,9 +35,9 @@ struct StepIO {
 };
 
 __device__ __forceinline__ int load_action(const void* a, int dt, long long idx) {
-  if (dt == 0) return (int)((const uint8_t*)a)[idx];
-  if (dt == 1) return ((const int*)a)[idx];
-  long long v = ((const long long*)a)[idx];
+  if (dt == 0) return (int)__ldg((const uint8_t*)a + idx);   // actions are read-only for the whole launch
+  if (dt == 1) return __ldg((const int*)a + idx);
+  long long v = __ldg((const long long*)a + idx);
   return (v < 0 || v > 3) ? -1 : (int)v;
 }
 

@@ -93,8 +93,9 @@ __device__ __forceinline__ void reset_tile_smem(const DevParams& p, int env, int
 // ------------------------------------------------------------------------------------------------ the kernel
 // MODE: 0 FULL obs, 1 WINDOW obs.  WC: compile-time window size (5) or 0 = runtime p.W.
 // FAST: the production configuration folded at compile time — all four stages in one pass (swarm_step / swarm_rollout),
-//       uint8 actions, collision_dist <= 0.5, no dwell counters, float32-exact coordinates.  FAST = false keeps every switch
-//       at run time (stage entry points, int32/int64 actions, cd > 0.5, dwell, exotic step sizes).
+//       collision_dist <= 0.5, no dwell counters, float32-exact coordinates; actions of any dtype (uint8 ones ride the stage's
+//       bulk copy, int32 / int64 — what torch's Categorical.sample() hands over — are read directly).  FAST = false keeps every
+//       switch at run time (stage entry points, cd > 0.5, dwell, exotic step sizes).
 // LEAN (implies FAST): additionally one step per launch (io.T == 1), N a multiple of the warp's env count, D == TS, obs and
 //       statistics requested, every per-group array on the TMA path (16-byte multiples for any whole number of groups) —
 //       checked by the host (launch_warp_ts).  Folds the rollout / alignment bookkeeping of the group loop away; the
@@ -140,7 +141,7 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
   const int WW = MODE == 1 ? (WC ? WC : p.W) * (WC ? WC : p.W) : 1;
   OT* const my_stage = stage + (tile * D + tl) * WW;
   // which per-group arrays may ride the bulk copy (size and address multiples of 16 B; planes, lists and meta always do)
-  const bool act_tma_ok = LEAN ? true : (flags & F_MOVE) && (FAST || io.act_dtype == 0) && (((uintptr_t)io.actions) & 15) == 0;
+  const bool act_tma_ok = LEAN ? true : (flags & F_MOVE) && io.act_dtype == 0 && (((uintptr_t)io.actions) & 15) == 0;
   const bool meta_tma = LEAN ? true : (flags & F_REWARD) != 0;
   // statistics accumulators are warp-uniform (REDUX results), so they live in uniform registers
   long long acc_rew = 0, acc_len = 0, acc_ret = 0;
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
     if (active) q = pos_tma ? reinterpret_cast<const float2*>(in + p.off_pos)[(wib * EPW + tile) * D + tl] : __ldcg(pp);
     if (active && (flags & F_MOVE)) {
       if (act_tma) a = (int)in[p.off_act + (wib * EPW + tile) * D + tl];
-      else a = FAST ? (int)__ldg((const uint8_t*)io.actions + aidx) : load_action(io.actions, io.act_dtype, (long long)aidx);
+      else a = load_action(io.actions, io.act_dtype, (long long)aidx);
     }
     if (valid && tl == 0) m = meta_tma ? reinterpret_cast<const int4*>(in + p.off_meta)[wib * EPW + tile] : make_int4(0, 0, 0, 0);
 
@@ -270,7 +271,7 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
       if (t > 0) a = a_next;   // rollout: positions / meta are carried in registers, actions are re-read
       if (!LEAN && t + 1 < T && active && (flags & F_MOVE)) {
         const size_t an = aidx + (size_t)N * D;
-        a_next = FAST ? (int)__ldg((const uint8_t*)io.actions + an) : load_action(io.actions, io.act_dtype, (long long)an);
+        a_next = FAST ? (int)__ldg((const uint8_t*)io.actions + an) : load_action(io.actions, io.act_dtype, (long long)an);   // FAST rollouts: uint8 (host-checked)
       }
 
       // ---- stage (1): action decode + move + clip (noVis_sim.py:117-135)

@@ -186,3 +186,29 @@ def test_action_dtypes_and_bad_action():
     with pytest.raises(AssertionError):
         g.step(torch.zeros((40, 7), dtype=torch.uint8, device="cuda"))
     g.close()
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg3", "cfg4"])
+def test_int_action_dtypes_take_the_fast_kernel_and_match(name):
+    """int32 / int64 actions (what torch's Categorical.sample() returns) run the FAST instantiation with direct action loads:
+    obs / reward / done / state equal the oracle's, step for step, negative and huge int64 codes included (error word)."""
+    kw = dict(SHAPES[name])
+    N, D = 333, kw["n_drones"]
+    g, o = make_pair(N, auto_reset=True, seed=17, **kw)
+    rs = np.random.RandomState(4)
+    for k in range(90):
+        a = rs.randint(0, 4, (N, D))
+        dt = (torch.int64, torch.int32, torch.uint8)[k % 3]
+        obs, rew, done, _ = g.step(torch.from_numpy(a).cuda().to(dt))
+        oo, orr, od = o.step(a.astype(np.uint8))
+        assert np.array_equal(obs.reshape(N, -1).cpu().numpy(), oo), (k, dt)
+        assert np.array_equal(rew.cpu().numpy(), orr) and np.array_equal(done.cpu().numpy(), od), (k, dt)
+    assert_state_equal(g, o)
+    assert g.device_error() == 0
+    before = g.pos.clone()
+    bad = torch.full((N, D), -1, dtype=torch.int64, device="cuda")
+    bad[0, 0] = 2 ** 40 + 1                    # the low byte alone would be a valid code
+    g.step(bad)
+    assert g.device_error() == 1
+    assert torch.equal(g.pos, before)          # an invalid code moves nothing
+    g.close()
