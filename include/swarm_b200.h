@@ -166,6 +166,14 @@ int swarm_rollout(SwarmEnv* env, int32_t T, const uint8_t* actions, void* obs_ou
 int swarm_step_host(SwarmEnv* env, const uint8_t* actions_host, void* obs_host,
                     float* reward_host, uint8_t* done_host, int64_t* stats_host, void* stream);
 
+/* swarm_step_host that also returns the positions after the step, float[N][D][2] — the reference's `env.n_drones_pos`, which
+ * its callers read after every step (A2C/train.py:54,81,229,266; DQL_model/DQLearning.py:166,173; A2C/a2c_eval.py:77,97).  One call
+ * is a whole `DroneEnv.step` as the single-env facade needs it.  For small batches (actions + obs + reward + done <= 64 KiB) both
+ * entry points hand PINNED host buffers to the kernel itself (it reads the actions and writes the results over PCIe), so the
+ * call costs one launch, the position copy and one synchronisation. */
+int swarm_step_host_pos(SwarmEnv* env, const uint8_t* actions_host, void* obs_host, float* reward_host,
+                        uint8_t* done_host, float* pos_host, int64_t* stats_host, void* stream);
+
 /* swarm_step_host without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
  * callers that cannot call cudaMalloc (code next to CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Same arguments, results and synchronisation as swarm_step_host, but the device-side staging of actions / obs / reward /

@@ -571,32 +571,68 @@ extern "C" int swarm_rollout(SwarmEnv* e, int32_t T, const uint8_t* actions, voi
   return launch_step(e, io, (cudaStream_t)stream);
 }
 
-extern "C" int swarm_step_host(SwarmEnv* e, const uint8_t* actions_host, void* obs_host, float* reward_host, uint8_t* done_host,
-                               int64_t* stats_host, void* stream) {
+// A PINNED host buffer (cudaHostAlloc / cudaHostRegister, torch's pin_memory) is addressable from the device under UVA.
+// Returns its device-side address, or null when the buffer is pageable.  Asked on every call (~1 us): a cached answer would go
+// stale when the caller frees the buffer.
+static void* host_mapped_ptr(const void* host) {
+  if (!host) return nullptr;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return (a.type == cudaMemoryTypeHost) ? a.devicePointer : nullptr;
+}
+
+// swarm_step_host / swarm_step_host_pos.  Two regimes:
+//  - large batches: H2D actions, step, D2H results through device staging — the copy engines move PCIe traffic faster than
+//    SM-issued stores do (measured);
+//  - SMALL batches (actions + obs + reward + done <= 64 KiB, e.g. the single-env facade the reference's scripts run on): the
+//    call is all fixed cost, so pinned host buffers are handed to the kernel itself — it reads the actions and writes obs /
+//    reward / done over PCIe — and the four copies with their launch latencies disappear (pageable buffers still stage).
+static int step_host_impl(SwarmEnv* e, const uint8_t* actions_host, void* obs_host, float* reward_host, uint8_t* done_host,
+                          float* pos_host, int64_t* stats_host, void* stream) {
   if (!e || !actions_host || !reward_host || !done_host) return SWARM_ERR_INVALID_ARG;
   int rc = use_device(e);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t N = (size_t)e->p.N, nact = N * e->p.D;
-  if (!e->h_act_dev) {
+  const size_t N = (size_t)e->p.N, nact = N * e->p.D, obs_bytes = obs_host ? (size_t)swarm_obs_bytes(e) : 0;
+  static const bool zc_off = getenv("SWARM_NO_ZEROCOPY") != nullptr;
+  const bool small = !zc_off && nact + obs_bytes + 5 * N <= (64u << 10);
+  const uint8_t* act_zc = small ? (const uint8_t*)host_mapped_ptr(actions_host) : nullptr;
+  void* obs_zc = small ? host_mapped_ptr(obs_host) : nullptr;
+  float* rew_zc = small ? (float*)host_mapped_ptr(reward_host) : nullptr;
+  uint8_t* done_zc = small ? (uint8_t*)host_mapped_ptr(done_host) : nullptr;
+  if (!e->h_act_dev && !(act_zc && rew_zc && done_zc)) {
     CUDA_TRY(cudaMalloc((void**)&e->h_act_dev, nact));
     CUDA_TRY(cudaMalloc((void**)&e->h_rew_dev, N * sizeof(float)));
     CUDA_TRY(cudaMalloc((void**)&e->h_done_dev, N));
   }
-  if (obs_host && !e->h_obs_dev) CUDA_TRY(cudaMalloc(&e->h_obs_dev, (size_t)swarm_obs_bytes(e)));
-  CUDA_TRY(cudaMemcpyAsync(e->h_act_dev, actions_host, nact, cudaMemcpyHostToDevice, st));
+  if (obs_host && !obs_zc && !e->h_obs_dev) CUDA_TRY(cudaMalloc(&e->h_obs_dev, obs_bytes));
+  if (!act_zc) CUDA_TRY(cudaMemcpyAsync(e->h_act_dev, actions_host, nact, cudaMemcpyHostToDevice, st));
   if (stats_host) CUDA_TRY(cudaMemsetAsync(e->stats_dev, 0, 64, st));
   StepIO io = make_io(F_ALL | (e->p.auto_reset ? F_RESET : 0));
-  io.actions = e->h_act_dev; io.act_dtype = SWARM_ACT_U8; io.obs_out = obs_host ? e->h_obs_dev : nullptr;
-  io.reward_out = e->h_rew_dev; io.done_out = e->h_done_dev; io.stats = stats_host ? e->stats_dev : nullptr;
+  io.actions = act_zc ? act_zc : e->h_act_dev; io.act_dtype = SWARM_ACT_U8;
+  io.obs_out = obs_host ? (obs_zc ? obs_zc : e->h_obs_dev) : nullptr;
+  io.reward_out = rew_zc ? rew_zc : e->h_rew_dev; io.done_out = done_zc ? done_zc : e->h_done_dev;
+  io.stats = stats_host ? e->stats_dev : nullptr;
   rc = launch_step(e, io, st);
   if (rc) return rc;
-  if (obs_host) CUDA_TRY(cudaMemcpyAsync(obs_host, e->h_obs_dev, (size_t)swarm_obs_bytes(e), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaMemcpyAsync(reward_host, e->h_rew_dev, N * sizeof(float), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaMemcpyAsync(done_host, e->h_done_dev, N, cudaMemcpyDeviceToHost, st));
+  if (obs_host && !obs_zc) CUDA_TRY(cudaMemcpyAsync(obs_host, e->h_obs_dev, obs_bytes, cudaMemcpyDeviceToHost, st));
+  if (!rew_zc) CUDA_TRY(cudaMemcpyAsync(reward_host, e->h_rew_dev, N * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (!done_zc) CUDA_TRY(cudaMemcpyAsync(done_host, e->h_done_dev, N, cudaMemcpyDeviceToHost, st));
+  if (pos_host) CUDA_TRY(cudaMemcpyAsync(pos_host, e->p.pos, nact * sizeof(float2), cudaMemcpyDeviceToHost, st));
   if (stats_host) CUDA_TRY(cudaMemcpyAsync(stats_host, e->stats_dev, 64, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
   return SWARM_OK;
+}
+
+extern "C" int swarm_step_host(SwarmEnv* e, const uint8_t* actions_host, void* obs_host, float* reward_host, uint8_t* done_host,
+                               int64_t* stats_host, void* stream) {
+  return step_host_impl(e, actions_host, obs_host, reward_host, done_host, nullptr, stats_host, stream);
+}
+
+extern "C" int swarm_step_host_pos(SwarmEnv* e, const uint8_t* actions_host, void* obs_host, float* reward_host, uint8_t* done_host,
+                                   float* pos_host, int64_t* stats_host, void* stream) {
+  if (!pos_host) return SWARM_ERR_INVALID_ARG;
+  return step_host_impl(e, actions_host, obs_host, reward_host, done_host, pos_host, stats_host, stream);
 }
 
 // ------------------------------------------------------------------------------------------------ stages

@@ -92,6 +92,7 @@ def lib():
         "swarm_rollout": (C.c_int, [vp, i32, vp, vp, i32, vp, vp, vp, vp]),
         "swarm_step_host": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
         "swarm_step_host_static": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+        "swarm_step_host_pos": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp]),
         "swarm_stage_move": (C.c_int, [vp, vp, C.c_int, vp]),
         "swarm_stage_scatter": (C.c_int, [vp, vp, vp]),
         "swarm_stage_reward": (C.c_int, [vp, vp, vp, vp, vp]),
@@ -135,7 +136,7 @@ EXPORTED = ("swarm_abi_version swarm_strerror swarm_last_cuda_error swarm_device
             "swarm_stage_obs swarm_greedy_actions swarm_device_error swarm_launch_count swarm_sample_actions "
             "swarm_nstep_returns swarm_gru_gates_fwd swarm_gru_gates_bwd swarm_bias_act swarm_embed_tanh_l2norm_fwd swarm_embed_tanh_l2norm_bwd swarm_row_standardize swarm_relu_l2norm_fwd swarm_relu_l2norm_bwd swarm_comm_unique_id swarm_comm_init swarm_comm_destroy swarm_stats_allreduce swarm_stats_mailbox_handle "
             "swarm_stats_peers_open swarm_stats_peers_close swarm_stats_global swarm_stats_global_host swarm_stats_push "
-            "swarm_step_host_static").split()
+            "swarm_step_host_static swarm_step_host_pos").split()
 
 
 def check(status):

@@ -143,6 +143,15 @@ class BatchedDroneEnv:
         check(self._L.swarm_step_host(self._h, hp(actions_host), hp(obs_host), hp(reward_host), hp(done_host),
                                       hp(stats_host), self._stream()))
 
+    def step_host_pos(self, actions_host, obs_host, reward_host, done_host, pos_host, stats_host=None):
+        """step_host that also returns the positions after the step (float32 [N, D, 2], the reference's `n_drones_pos`)."""
+        def hp(a):
+            if a is None:
+                return None
+            return C.c_void_p(a.data_ptr() if torch.is_tensor(a) else a.ctypes.data)
+        check(self._L.swarm_step_host_pos(self._h, hp(actions_host), hp(obs_host), hp(reward_host), hp(done_host),
+                                          hp(pos_host), hp(stats_host), self._stream()))
+
     def step_host_static(self, actions_host, obs_host, reward_host, done_host, stats_host=None):
         """step_host through swarm_step_host_static: the device-side staging is the library's fixed static array
         (SWARM_STATIC_SCRATCH_BYTES), so the call allocates nothing; sizes beyond it raise SwarmError.  No counterpart in

@@ -3,13 +3,17 @@
 (`action_size`, `state_size`, `n_drones`, `n_drones_pos`, `uncertain_points`, `grid`, `step_func_count`;
 A2C/main.py:105-107, A2C/train.py:54,81,229,266, A2C/a2c_eval.py:77,92,97, DQL_model/Agent_test.py:168).
 
-The env itself lives on the GPU (a BatchedDroneEnv of one env, auto_reset off); every step is one kernel launch plus
-one device->host read.  `reset()` draws from the GLOBAL legacy `np.random` stream in the reference's order
+The env itself lives on the GPU (a BatchedDroneEnv of one env, auto_reset off); every step is ONE C-ABI call
+(`swarm_step_host_pos`: one kernel launch that reads the pinned action buffer and writes obs / reward / done into pinned host
+memory, the position copy, one synchronisation).  `reset()` draws from the GLOBAL legacy `np.random` stream in the reference's order
 (A2C/noVis_sim.py:47-49,59-61), so `np.random.seed(s)` reproduces the reference's resets bit for bit.
 """
+import ctypes as C
+
 import numpy as np
 import torch
 
+from ._lib import check
 from .batched import BatchedDroneEnv
 
 
@@ -26,12 +30,21 @@ class DroneEnv:
         self.step_func_count = 0
         self._env = BatchedDroneEnv(1, row_count, col_count, n_anamolous, uncertainity, collision_dist, n_drones, step_size,
                                     reward_mode=self.reward_mode, obs_mode="full", obs_dtype=torch.uint8, auto_reset=False)
-        dev = self._env.device
-        self._act = torch.zeros((1, n_drones), dtype=torch.uint8, device=dev)
-        self._act_host = torch.zeros((1, n_drones), dtype=torch.uint8).pin_memory()
-        # one packed device->host record per step: obs bytes | reward f32 | done u8 (pad) | pos f32
-        self._rec = torch.zeros(self.state_size + 8 + 8 * n_drones, dtype=torch.uint8, device=dev)
-        self._rec_host = torch.zeros_like(self._rec, device="cpu").pin_memory()
+        # pinned host buffers of ONE swarm_step_host_pos call: at this size the kernel reads the actions and writes obs / reward /
+        # done straight over PCIe, so a step is one launch, the position copy and one synchronisation
+        pin = lambda shape, dt: torch.zeros(shape, dtype=dt).pin_memory()
+        self._act_host, self._obs_host = pin((1, n_drones), torch.uint8), pin(self.state_size, torch.uint8)
+        self._rew_host, self._done_host = pin(1, torch.float32), pin(1, torch.uint8)
+        self._pos_host = pin((n_drones, 2), torch.float32)
+        self._act_np, self._obs_np, self._pos_np = self._act_host.numpy(), self._obs_host.numpy(), self._pos_host.numpy()
+        self._rew_np, self._done_np = self._rew_host.numpy(), self._done_host.numpy()
+        L, h = self._env._L, self._env._h
+        ptrs = [C.c_void_p(t.data_ptr()) for t in (self._act_host, self._obs_host, self._rew_host, self._done_host, self._pos_host)]
+        dev_index = self._env.device.index
+        def step_call():
+            check(L.swarm_step_host_pos(h, ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], None,
+                                        C.c_void_p(torch.cuda.current_stream(dev_index).cuda_stream)))
+        self._step_call = step_call
         self._obs_u8 = np.ones(self.state_size, np.uint8)
         self.n_drones_pos = None
         self.uncertain_points = None
@@ -68,25 +81,15 @@ class DroneEnv:
 
     def step(self, actions):
         assert len(actions) == self.n_drones, "provide actions for each drone"
-        host = self._act_host
+        host = self._act_np
         for i, action in enumerate(actions):
             assert action >= 0 and action < self.action_size, f"action should be in range:[0,{self.action_size})"
             host[0, i] = int(np.asarray(action).reshape(-1)[0])
-        self._act.copy_(host, non_blocking=True)
-        obs, rew, done, _ = self._env.step(self._act)
-        n = self.state_size
-        rec = self._rec
-        rec[:n] = obs.view(-1)
-        rec[n:n + 4] = rew.view(torch.uint8)
-        rec[n + 4:n + 5] = done
-        rec[n + 8:] = self._env.pos.view(-1).view(torch.uint8)
-        self._rec_host.copy_(rec, non_blocking=True)
-        torch.cuda.current_stream(self._env.device).synchronize()
-        r = self._rec_host.numpy()
-        self._obs_u8 = r[:n].copy()
-        reward = float(r[n:n + 4].view(np.float32)[0])
-        done_b = bool(r[n + 4])
-        self._set_pos(r[n + 8:].view(np.float32).reshape(self.n_drones, 2))
+        self._step_call()                       # H2D (or direct read), the fused step, obs / reward / done / positions back, sync
+        self._obs_u8 = self._obs_np.copy()
+        reward = float(self._rew_np[0])
+        done_b = bool(self._done_np[0])
+        self._set_pos(self._pos_np)
         self.step_func_count += 1
         for k in self.uncertain_points:
             if self.uncertain_points[k] == 1 and self._obs_u8[k[1] * self.row_count + k[0]] == 0:
