@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from ._lib import check
-from .batched import BatchedDroneEnv
+from .batched import BatchedDroneEnv, _raw_stream
 
 
 class DroneEnv:
@@ -38,12 +38,13 @@ class DroneEnv:
         self._pos_host = pin((n_drones, 2), torch.float32)
         self._act_np, self._obs_np, self._pos_np = self._act_host.numpy(), self._obs_host.numpy(), self._pos_host.numpy()
         self._rew_np, self._done_np = self._rew_host.numpy(), self._done_host.numpy()
-        L, h = self._env._L, self._env._h
+        fn, h = self._env._L.swarm_step_host_pos, self._env._h
         ptrs = [C.c_void_p(t.data_ptr()) for t in (self._act_host, self._obs_host, self._rew_host, self._done_host, self._pos_host)]
         dev_index = self._env.device.index
         def step_call():
-            check(L.swarm_step_host_pos(h, ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], None,
-                                        C.c_void_p(torch.cuda.current_stream(dev_index).cuda_stream)))
+            rc = fn(h, ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], None, _raw_stream(dev_index))
+            if rc:
+                check(rc)
         self._step_call = step_call
         self._obs_u8 = np.ones(self.state_size, np.uint8)
         self.n_drones_pos = None
@@ -84,7 +85,7 @@ class DroneEnv:
         host = self._act_np
         for i, action in enumerate(actions):
             assert action >= 0 and action < self.action_size, f"action should be in range:[0,{self.action_size})"
-            host[0, i] = int(np.asarray(action).reshape(-1)[0])
+            host[0, i] = action if type(action) is int else int(np.asarray(action).reshape(-1)[0])
         self._step_call()                       # H2D (or direct read), the fused step, obs / reward / done / positions back, sync
         self._obs_u8 = self._obs_np.copy()
         reward = float(self._rew_np[0])
