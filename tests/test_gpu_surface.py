@@ -141,17 +141,19 @@ def test_step_host_large_obs_matches_device_step(name, N):
     host.close(); dev.close()
 
 
-@pytest.mark.parametrize("N,name,pinned", [(1, "cfg1", True), (7, "cfg4", True), (16, "cfg3", True), (5, "cfg2", False), (300, "cfg4", True)])
-def test_step_host_pos_small_batches_match_oracle(N, name, pinned):
+@pytest.mark.parametrize("N,name,pinned,odt", [(1, "cfg1", True, torch.uint8), (7, "cfg4", True, torch.uint8), (16, "cfg3", True, torch.uint8),
+                                               (5, "cfg2", False, torch.uint8), (300, "cfg4", True, torch.uint8),
+                                               (3, "cfg1", True, torch.float32), (9, "cfg3", True, torch.float32), (2, "cfg5b", True, torch.float32)])
+def test_step_host_pos_small_batches_match_oracle(N, name, pinned, odt):
     """swarm_step_host_pos (what the single-env facade calls): small batches hand pinned host buffers to the kernel itself
     (actions read and results written over PCIe), pageable ones and larger batches stage and copy; all equal the oracle, and the
     positions returned equal the resident ones."""
     kw = dict(SHAPES[name])
     D = kw["n_drones"]
-    g, o = make_pair(N, auto_reset=True, seed=5, obs_dtype=torch.uint8, **kw)
+    g, o = make_pair(N, auto_reset=True, seed=5, obs_dtype=odt, **kw)
     mk = (lambda t: t.pin_memory()) if pinned else (lambda t: t)
     a_h = mk(torch.empty((N, D), dtype=torch.uint8))
-    obs_h = mk(torch.empty(g.obs_shape, dtype=torch.uint8))
+    obs_h = mk(torch.empty(g.obs_shape, dtype=odt))
     rew_h, done_h = mk(torch.empty(N, dtype=torch.float32)), mk(torch.empty(N, dtype=torch.uint8))
     pos_h = mk(torch.empty((N, D, 2), dtype=torch.float32))
     stats_h = mk(torch.zeros(8, dtype=torch.int64))
@@ -162,7 +164,8 @@ def test_step_host_pos_small_batches_match_oracle(N, name, pinned):
         obs_h.fill_(77); pos_h.fill_(-3)
         g.step_host_pos(a_h, obs_h, rew_h, done_h, pos_h, stats_h if k % 2 else None)
         oo, orr, od = o.step(a)
-        assert np.array_equal(obs_h.numpy().reshape(N, -1), oo.astype(np.int16).astype(np.uint8)), k
+        want = oo.astype(np.int16).astype(np.uint8) if odt == torch.uint8 else oo.astype(np.float32)   # pad -1 -> 255 for uint8
+        assert np.array_equal(obs_h.numpy().reshape(N, -1), want), k
         assert np.array_equal(rew_h.numpy(), orr) and np.array_equal(done_h.numpy(), od), k
         assert np.array_equal(pos_h.numpy().astype(np.float64), o.pos), k
         if k % 2:
