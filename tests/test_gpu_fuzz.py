@@ -1,6 +1,8 @@
 """GPU: seeded random configurations (shape, drones, step size, collision distance, obs mode / window / dtype, anomalies incl. PLANE
 mode, reward variant, auto-reset, dwell, action dtype, env count) in lock-step against the oracle: obs, reward, done every step,
 full state and statistics at the end.  The configurations are drawn once from a fixed seed, so a failure names its case."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -28,7 +30,8 @@ def draw_cases(n=160, seed=2026):
     return cases
 
 
-CASES = draw_cases()
+# SWARM_FUZZ_N / SWARM_FUZZ_SEED widen the hunt for one-off runs (e.g. SWARM_FUZZ_N=2000 SWARM_FUZZ_SEED=7 pytest tests/test_gpu_fuzz.py)
+CASES = draw_cases(int(os.environ.get("SWARM_FUZZ_N", 160)), int(os.environ.get("SWARM_FUZZ_SEED", 2026)))
 
 
 @pytest.mark.parametrize("case", CASES, ids=[f"case{c[0]}" for c in CASES])
@@ -52,7 +55,7 @@ def test_fuzz_lockstep(case):
     g.close()
 
 
-ROLLOUT_CASES = draw_cases(n=48, seed=77)
+ROLLOUT_CASES = draw_cases(max(48, int(os.environ.get("SWARM_FUZZ_N", 160)) // 4), int(os.environ.get("SWARM_FUZZ_SEED", 2026)) + 51)
 
 
 @pytest.mark.parametrize("case", ROLLOUT_CASES, ids=[f"case{c[0]}" for c in ROLLOUT_CASES])
