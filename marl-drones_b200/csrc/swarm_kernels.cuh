@@ -145,6 +145,61 @@ __global__ void __launch_bounds__(256) move_kernel(const __grid_constant__ DevPa
 // reference steps +-1 on both axes at once, which the noVis action set cannot express): the axis with the larger |delta|.
 // Distances: the reference compares ((dx)**2 + (dy)**2) ** 0.5; on the lattice (multiples of 2^-k) the squares are exact and
 // sqrt is strictly monotone on them at these magnitudes, so comparing the squared distances picks the same cell.
+//
+// The scan itself is NOT the reference's R*C loop (4.3 ms per call at cfg3): the winner of that loop is the cell with the smallest
+// key (d2, gx, gy) — strict `>` keeps the first of equal distances, and the scan order is gx-major — so any order of evaluation
+// finds it.  Rows are visited outward from the drone's row (offset j: cy - j, cy + j); in a row only the nearest unmapped cell on
+// each side of x can win, found per 32-cell word with CLZ / FFS; the search stops once (j - 0.5)^2 exceeds the best d2 (no row
+// further out can even tie).  The quirk: a drone standing exactly on an unmapped cell c0 ends up with the nearest cell AFTER c0
+// in scan order (gx > x0, or gx == x0 and gy > y0), or with c0 itself when there is none — the same search with a lower bound
+// on gx per row.
+struct GreedyBest {
+  double d2;
+  int gx, gy;
+  __device__ __forceinline__ void consider(int x_, int y_, double x, double y) {
+    const double dx = x_ - x, dy = y_ - y, d = dx * dx + dy * dy;
+    if (gx < 0 || d < d2 || (d == d2 && (x_ < gx || (x_ == gx && y_ < gy)))) { d2 = d; gx = x_; gy = y_; }
+  }
+};
+
+// One 32-cell word `w` (word index k of the plane) of row gy = bits [s, s + R): feeds the unmapped cells nearest to `t`
+// (= floor(x)) on both sides into `best`, among cells with gx >= gmin.
+__device__ __forceinline__ void greedy_word(uint32_t w, int k, int s, int R, int gy, int t, int gmin, double x, double y, GreedyBest& best) {
+  const int base = k * 32 - s;                         // gx of bit 0 of this word
+  const int lo = max(max(s - k * 32, 0), gmin - base), hi = min(s + R - k * 32, 32);
+  if (lo >= hi) return;
+  w &= (hi == 32 ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);   // lo < 32 here
+  if (!w) return;
+  const int tw = t - base;                             // t in word coordinates
+  const uint32_t left = tw >= 31 ? w : (tw < 0 ? 0u : (w & ((2u << tw) - 1u)));
+  const uint32_t right = w & ~left;
+  if (left) best.consider(base + 31 - __clz(left), gy, x, y);
+  if (right) best.consider(base + __ffs(right) - 1, gy, x, y);
+}
+
+// Row gy of the env's plane `g` (any alignment; rows of whole 128-cell chunks are read 16 bytes at a time and empty chunks —
+// most of a late-episode grid — cost one test).
+__device__ __forceinline__ void greedy_row(const uint32_t* __restrict__ g, int R, int gy, int t, int gmin, double x, double y, GreedyBest& best) {
+  const int s = gy * R;
+  if ((R & 127) == 0) {
+    const uint4* g4 = reinterpret_cast<const uint4*>(g) + (s >> 7);
+    for (int c = 0; c < (R >> 7); ++c) {
+      const uint4 v = __ldg(g4 + c);
+      if (!(v.x | v.y | v.z | v.w)) continue;
+      const int k = (s >> 5) + 4 * c;
+      if (v.x) greedy_word(v.x, k, s, R, gy, t, gmin, x, y, best);
+      if (v.y) greedy_word(v.y, k + 1, s, R, gy, t, gmin, x, y, best);
+      if (v.z) greedy_word(v.z, k + 2, s, R, gy, t, gmin, x, y, best);
+      if (v.w) greedy_word(v.w, k + 3, s, R, gy, t, gmin, x, y, best);
+    }
+    return;
+  }
+  for (int k = s >> 5; k <= (s + R - 1) >> 5; ++k) {
+    const uint32_t w = __ldg(g + k);
+    if (w) greedy_word(w, k, s, R, gy, t, gmin, x, y, best);
+  }
+}
+
 __global__ void __launch_bounds__(256) greedy_kernel(const __grid_constant__ DevParams p, uint8_t* actions) {
   const long long n = (long long)p.N * p.D;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -152,17 +207,24 @@ __global__ void __launch_bounds__(256) greedy_kernel(const __grid_constant__ Dev
     const uint32_t* g = p.cov + (size_t)env * p.env_words;
     const float2 q = p.pos[i];
     const double x = q.x, y = q.y;
-    double best = 0.0;
-    bool have = false;
-    int bx = -1, by = -1;
-    for (int gx = 0; gx < p.R; ++gx)
-      for (int gy = 0; gy < p.C; ++gy) {
-        const int cell = gy * p.R + gx;
-        if ((ld_grid(g + (cell >> 5)) >> (cell & 31)) & 1u) {
-          const double d2 = (gx - x) * (gx - x) + (gy - y) * (gy - y);
-          if (!have || best == 0.0 || d2 < best) { have = true; best = d2; bx = gx; by = gy; }
-        }
-      }
+    const int cx = (int)floorf(q.x + 0.5f), cy = (int)floorf(q.y + 0.5f), t = (int)floorf(q.x);
+    // does the drone stand exactly on an unmapped cell?  (then only cells after it in scan order compete)
+    bool on_cell = false;
+    if ((float)cx == q.x && (float)cy == q.y) {
+      const int c0 = cy * p.R + cx;
+      on_cell = (__ldg(g + (c0 >> 5)) >> (c0 & 31)) & 1u;
+    }
+    GreedyBest best;
+    best.d2 = 0.0; best.gx = -1; best.gy = -1;
+    const int jmax = p.meta[env].y == 0 ? -1 : max(cy, p.C - 1 - cy);   // nothing left to map: no search (action 0)
+    for (int j = 0; j <= jmax; ++j) {
+      if (j > 0 && best.gx >= 0 && ((double)j - 0.5) * ((double)j - 0.5) > best.d2) break;   // rows at offset >= j: d2 >= (j - 0.5)^2
+      const int ya = cy - j, yb = cy + j;
+      if (ya >= 0) greedy_row(g, p.R, ya, t, on_cell ? cx + 1 : 0, x, y, best);                       // gy <= y0: gx > x0
+      if (j > 0 && yb < p.C) greedy_row(g, p.R, yb, t, on_cell ? cx : 0, x, y, best);                 // gy > y0: gx >= x0
+    }
+    int bx = best.gx, by = best.gy;
+    if (bx < 0 && on_cell) { bx = cx; by = cy; }       // nothing after c0: the running minimum stays c0
     uint8_t a = 0;
     if (bx >= 0) {
       const double dx = bx - x, dy = by - y;

@@ -87,3 +87,29 @@ def test_fuzz_rollout(case):
     assert np.array_equal(g.stats.cpu().numpy(), o.stats), kw
     assert g.device_error() == 0
     g.close()
+
+
+GREEDY_CASES = draw_cases(n=64, seed=4242)
+
+
+@pytest.mark.parametrize("case", GREEDY_CASES, ids=[f"case{c[0]}" for c in GREEDY_CASES])
+def test_fuzz_greedy_actions(case):
+    """swarm_greedy_actions (row-outward word search) against the oracle's literal R*C scan of drone.py on random shapes: fresh
+    envs (every drone stands on an unmapped cell: the `if not min_dist` quirk), fractional positions, nearly and fully mapped grids;
+    greedy and random moves alternate so that the states vary."""
+    i, N, adt, kw = case
+    kw = dict(kw)
+    kw["auto_reset"] = bool(i % 2)
+    g, o = make_pair(N, seed=900 + i, **kw)
+    rs = np.random.RandomState(i)
+    D = o.D
+    steps = 30 + 4 * min(kw["row_count"] * kw["col_count"], 60)
+    for k in range(steps):
+        a = g.greedy_actions()
+        assert np.array_equal(a.cpu().numpy(), o.greedy_actions()), (kw, N, k)
+        if k % 5 == 4:
+            a = torch.from_numpy(rs.randint(0, 4, (N, D)).astype(np.uint8)).cuda()
+        g.step(a, want_obs=False)
+        o.step(a.cpu().numpy())
+    assert_state_equal(g, o, str(kw))
+    g.close()
