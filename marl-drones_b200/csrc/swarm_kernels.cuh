@@ -123,8 +123,15 @@ __global__ void __launch_bounds__(256) set_state_kernel(const __grid_constant__ 
     if (pos)
       for (int k = lane; k < p.D; k += 32)
         p.pos[(size_t)env * p.D + k] = make_float2(pos[((size_t)e * p.D + k) * 2], pos[((size_t)e * p.D + k) * 2 + 1]);
-    if (wait && p.has_wait)
-      for (int k = lane; k < p.RC; k += 32) p.wait[(size_t)env * p.RC + k] = wait[(size_t)e * p.RC + k];
+    if (wait && p.has_wait) {
+      if ((p.RC & 7) == 0 && (((uintptr_t)wait) & 15) == 0) {   // eight counters per access
+        const uint4* s4 = reinterpret_cast<const uint4*>(wait + (size_t)e * p.RC);
+        uint4* d4 = reinterpret_cast<uint4*>(p.wait + (size_t)env * p.RC);
+        for (int k = lane; k < (p.RC >> 3); k += 32) d4[k] = __ldg(s4 + k);
+      } else {
+        for (int k = lane; k < p.RC; k += 32) p.wait[(size_t)env * p.RC + k] = wait[(size_t)e * p.RC + k];
+      }
+    }
     if (lane == 0) {
       int4 m = p.meta[env];
       if (t) m.x = t[e];
@@ -185,8 +192,15 @@ __global__ void __launch_bounds__(256) get_state_kernel(const __grid_constant__ 
         pos[((size_t)e * p.D + k) * 2] = q.x;
         pos[((size_t)e * p.D + k) * 2 + 1] = q.y;
       }
-    if (wait)
-      for (int k = lane; k < p.RC; k += 32) wait[(size_t)e * p.RC + k] = p.has_wait ? p.wait[(size_t)env * p.RC + k] : (int16_t)0;
+    if (wait) {
+      if ((p.RC & 7) == 0 && (((uintptr_t)wait) & 15) == 0) {   // eight counters per access
+        const uint4* s4 = p.has_wait ? reinterpret_cast<const uint4*>(p.wait + (size_t)env * p.RC) : nullptr;
+        uint4* d4 = reinterpret_cast<uint4*>(wait + (size_t)e * p.RC);
+        for (int k = lane; k < (p.RC >> 3); k += 32) d4[k] = s4 ? s4[k] : make_uint4(0u, 0u, 0u, 0u);
+      } else {
+        for (int k = lane; k < p.RC; k += 32) wait[(size_t)e * p.RC + k] = p.has_wait ? p.wait[(size_t)env * p.RC + k] : (int16_t)0;
+      }
+    }
     if (t && lane == 0) t[e] = p.meta[env].x;
   }
 }
