@@ -73,3 +73,22 @@ def test_no_cpu_fallback():
     src = "".join(open(os.path.join(REPO, "marl-drones_b200", "swarm_b200", f)).read()
                   for f in os.listdir(os.path.join(REPO, "marl-drones_b200", "swarm_b200")) if f.endswith(".py"))
     assert "oracle" not in src.replace("never route to the oracle", ""), "product code must not reference the oracle"
+
+
+def test_hot_kernel_sass_carries_what_the_design_claims():
+    """The cfg3 LEAN instantiation in the in-tree library really uses what DESIGN.md §4.1 names (cuobjdump, no GPU needed):
+    TMA bulk loads and the bulk obs store, mbarrier waits, the shared-memory atomics, the warp-wide reduction and the
+    programmatic-dependent-launch pair (griddepcontrol.wait = ACQBULK, griddepcontrol.launch_dependents = PREEXIT)."""
+    import shutil
+    import subprocess
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not available")
+    _lib.lib()                                                   # builds the library if it is missing
+    name = "_ZN5swarm16step_warp_kernelILi16EfLi1ELi5ELb1ELb1EEEvNS_9DevParamsENS_6StepIOE"
+    sass = subprocess.run([exe, "-sass", "-fun", name, _lib.SO_PATH], capture_output=True, text=True).stdout
+    assert "Function : " + name in sass and "sm_100a" in sass
+    for op, at_least in (("UBLKCP.S.G", 4), ("UBLKCP.G.S", 1), ("SYNCS.PHASECHK.TRANS64.TRYWAIT", 1), ("ATOMS.AND", 1), ("REDUX.SUM", 1),
+                         ("ACQBULK", 2), ("PREEXIT", 1)):
+        assert sass.count(op) >= at_least, (op, sass.count(op))
+    assert "tcgen05" not in sass.lower()                         # no stage of this path is a dense contraction
