@@ -865,8 +865,9 @@ def main():
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + [A2C_WORKLOAD, DQL_WORKLOAD])
     ap.add_argument("--rollout-steps", type=int, default=25, help="cfg4_a2c: env steps per outer iteration (A2C/main.py default)")
     ap.add_argument("--tf32", action="store_true", help="cfg4_a2c: allow TF32 tensor-core GEMMs for the policy (default: fp32, as the reference)")
-    ap.add_argument("--obs-dtype", default="float32", choices=["float32", "uint8"],
-                    help="observation element type of the device-timed step (default float32 = the reference's; uint8 is a diagnostic line)")
+    ap.add_argument("--obs-dtype", default="float32", choices=["float32", "uint8", "packed2"],
+                    help="observation element type of the device-timed step (default float32 = the reference's; uint8 and packed2 — "
+                         "5x5 windows as one 64-bit word per drone — are diagnostic lines)")
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--sets", type=int, default=4, help="independent env batches rotated so the working set exceeds L2")
@@ -918,8 +919,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     D = kw["n_drones"]
     K, W = max(args.steps, 1), max(args.warmup, 3)
-    obs_dt = torch.float32 if args.obs_dtype == "float32" else torch.uint8
-    s_o = 4 if args.obs_dtype == "float32" else 1
+    obs_dt = {"float32": torch.float32, "uint8": torch.uint8, "packed2": torch.int64}[args.obs_dtype]
+    s_o = {"float32": 4, "uint8": 1, "packed2": 8.0 / 25.0}[args.obs_dtype]      # bytes per obs cell
     loop = StepLoop(torch, dev, n_envs, kw, args.sets, obs_dt, rank * args.sets * n_envs, rank, use_graph=not args.no_graph)
     envs, n_act = loop.envs, loop.N_ACT
     stream = torch.cuda.current_stream(dev)
@@ -1037,7 +1038,7 @@ def main():
                                 ms_total / K if world == 1 else None, loop, rollout)
 
     floor_us = launch_floor_us(torch, dev)
-    moved = real_bytes_per_env_step(kw, s_o=s_o) * n_envs          # what the resident layout really moves per launch
+    moved = int(real_bytes_per_env_step(kw, s_o=s_o) * n_envs)     # what the resident layout really moves per launch
     copy_us, copy_bytes = copy_same_bytes_us(torch, dev, moved)
     # ---- e2e: host buffers through swarm_step_host (H2D actions + D2H obs/reward/done inside the timed region).
     # Headline format: uint8 observations (values 0 / 1 / U, pad 255) — the reference's obs are small integers (int64 on the
@@ -1052,6 +1053,15 @@ def main():
     ef_ms, ef_d2h = measure_e2e(torch, dist, dev, world, ef, a_h, torch.float32, E)
     if ef is not envs[0]:
         ef.close()
+    # the packed 2-bit window format (SWARM_DTYPE_P2, 8 B per drone): reported beside the headline, never as it
+    ep_ms = ep_d2h = None
+    if kw.get("obs_mode") == "window" and kw.get("window") == 5 and D <= 32:
+        try:
+            ep = BatchedDroneEnv(n_envs, auto_reset=True, seed=2026, env_id_base=rank * args.sets * n_envs, obs_dtype="packed2", **kw)
+            ep_ms, ep_d2h = measure_e2e(torch, dist, dev, world, ep, a_h, torch.int64, E)
+            ep.close()
+        except Exception as exc:                    # every rank takes the same branch: creation depends on the shape only
+            print(f"[bench] packed2 e2e skipped: {exc!r}", file=sys.stderr)
     h2d = n_envs * D
     agent_e2e = float(n_envs) * D * E * world
 
@@ -1082,7 +1092,7 @@ def main():
 
     if rank == 0:
         peak, peak_src = load_peak()
-        bytes_per_launch = algorithmic_bytes_per_env_step(kw, s_o=s_o) * n_envs
+        bytes_per_launch = int(algorithmic_bytes_per_env_step(kw, s_o=s_o) * n_envs)
         achieved = bytes_per_launch / (kern_avg_ms * 1e-3) / 1e9
         e0 = envs[0]
         line = {
@@ -1092,7 +1102,7 @@ def main():
             "config": {"workload": args.workload, "envs_per_gpu": n_envs, "total_envs": n_envs * world, **kw,
                        "obs_dtype": args.obs_dtype, "auto_reset": True, "reward_mode": "A2C", "reset_rng": "philox4x32-10",
                        "actions": "uint8 uniform{0..3} (16 draws + their opposites, zero net drift), pre-generated on device",
-                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * s_o + n_envs * 700) / 1e6:.0f} MB > 126 MB L2",
+                       "l2": f"{args.sets} independent env batches rotated; working set {args.sets * (e0._obs.numel() * e0._obs.element_size() + n_envs * 700) / 1e6:.0f} MB > 126 MB L2",
                        "parallelism": f"env-sharded x{world}, no data-path collective; per-step episode statistics: " +
                                       ("published by the step kernel into every rank's mailbox over NVLink peer memory (posted stores at kernel start, no collective kernel)"
                                        if not use_nccl else f"swarm_stats_allreduce (NCCL) on a side stream every {max(args.stats_every, 1)} step(s)")},
@@ -1113,6 +1123,11 @@ def main():
             "e2e_float32_obs": {"value": agent_e2e / (ef_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": ef_d2h,
                                 "steps": E, "ms_per_step": ef_ms / E, "obs_format": "float32 (what the reference's callers cast to)",
                                 "d2h_gbs_per_rank": ef_d2h / (ef_ms / E * 1e-3) / 1e9},
+            "e2e_packed2_obs": None if ep_ms is None else {
+                "value": agent_e2e / (ep_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": ep_d2h, "steps": E,
+                "ms_per_step": ep_ms / E, "d2h_gbs_per_rank": ep_d2h / (ep_ms / E * 1e-3) / 1e9,
+                "obs_format": "packed 2-bit windows (SWARM_DTYPE_P2: one uint64 per drone = two bit planes of its 5x5 window, lossless; "
+                              "swarm_b200.unpack_windows expands it) — an extra line for consumers that take the packed form, not the headline"},
             "rollout": rollout, "launch_floor_us": floor_us,
             "same_size_copy": {"us": copy_us, "bytes": copy_bytes, "gbs": copy_bytes / (copy_us * 1e-6) / 1e9,
                                "step_over_copy": (ms_total / K * 1e3) / copy_us,

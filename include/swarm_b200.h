@@ -35,6 +35,7 @@
  *  - dwell counters     int16 [N][C][R]   only when dwell_normal|dwell_anom != 0
  *  - obs FULL           T     [N][R*C]    obs[n][y*R+x]                (T = float32 or uint8)
  *  - obs WINDOW         T     [N][D][W*W] win[n][i][b*W+a] = grid[cx-h+a][cy-h+b], pad -1 (255 for uint8)
+ *  - obs WINDOW packed  u64   [N][D]      SWARM_DTYPE_P2: the 25 cells of a 5x5 window as two bit planes in one word (see the enum)
  *  - resident coverage map (private): 1 bit / cell (1 = still unmapped), 32 cells per uint32, flat index y*R+x, plus the
  *    env's anomalous cells as a list of 8 x uint32 (x | y << 16) or, for more than 8 anomalies / sides > 256, a second plane.
  */
@@ -62,7 +63,13 @@ typedef enum SwarmStatus {
 
 enum { SWARM_REWARD_A2C = 0, SWARM_REWARD_DQL = 1 };   /* A2C/noVis_sim.py:141-152,172-173 vs DQL_model/noVis_sim.py:138-148 */
 enum { SWARM_OBS_FULL = 0, SWARM_OBS_WINDOW = 1 };     /* A2C/noVis_sim.py:168-170 vs SURVEY App. B.1 */
-enum { SWARM_DTYPE_F32 = 0, SWARM_DTYPE_U8 = 1 };      /* obs element type */
+enum { SWARM_DTYPE_F32 = 0, SWARM_DTYPE_U8 = 1,        /* obs element type */
+       SWARM_DTYPE_P2 = 2 };  /* packed 2-bit windows (WINDOW mode, W = 5, shapes the staged warp kernel serves: D <= 32, <= 8 anomalies,
+                               * sides <= 256; anything else is SWARM_ERR_CONFIG): ONE uint64 per drone, obs uint64 [N][D].  For window
+                               * cell k = b*5 + a (the layout of the WINDOW obs above): bit k = LO, bit 32 + k = HI, code = LO + 2 HI:
+                               * 0 mapped -> 0, 1 unmapped -> 1, 3 unmapped and anomalous -> uncertainity, 2 outside the grid -> -1 (255).
+                               * Lossless, 12.5x smaller than the float32 windows (8 B instead of 100 B per drone): the form for
+                               * device-side consumers and for host links that are PCIe-bound; `swarm_b200.unpack_windows` expands it. */
 enum { SWARM_ACT_U8 = 0, SWARM_ACT_I32 = 1, SWARM_ACT_I64 = 2 };
 
 /* device error word bits (sticky until swarm_device_error(clear=1)) */

@@ -81,7 +81,8 @@ constexpr int kWarpSmemMax = 20 * 1024;     // per-warp shared-memory slice the 
 
 static int stage_bytes_for(const SwarmConfig* c, int epw) {
   if (c->obs_mode != SWARM_OBS_WINDOW) return 16;
-  const long long b = (long long)epw * c->n_drones * c->window * c->window * (c->obs_dtype == SWARM_DTYPE_F32 ? 4 : 1);
+  const long long b = c->obs_dtype == SWARM_DTYPE_P2 ? (long long)epw * c->n_drones * 8   // one packed word per drone
+                                                      : (long long)epw * c->n_drones * c->window * c->window * (c->obs_dtype == SWARM_DTYPE_F32 ? 4 : 1);
   return (int)((b + 15) / 16 * 16);
 }
 
@@ -137,7 +138,8 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   if (c->reward_mode != SWARM_REWARD_A2C && c->reward_mode != SWARM_REWARD_DQL) return SWARM_ERR_CONFIG;
   if (c->obs_mode != SWARM_OBS_FULL && c->obs_mode != SWARM_OBS_WINDOW) return SWARM_ERR_CONFIG;
   if (c->obs_mode == SWARM_OBS_WINDOW && (c->window < 1 || c->window > 31 || (c->window & 1) == 0)) return SWARM_ERR_CONFIG;
-  if (c->obs_dtype != SWARM_DTYPE_F32 && c->obs_dtype != SWARM_DTYPE_U8) return SWARM_ERR_CONFIG;
+  if (c->obs_dtype != SWARM_DTYPE_F32 && c->obs_dtype != SWARM_DTYPE_U8 && c->obs_dtype != SWARM_DTYPE_P2) return SWARM_ERR_CONFIG;
+  if (c->obs_dtype == SWARM_DTYPE_P2 && (c->obs_mode != SWARM_OBS_WINDOW || c->window != 5)) return SWARM_ERR_CONFIG;   // packed: 5x5 windows only
   if (!(c->collision_dist >= 0.0) || c->collision_dist > 64.0 || !(c->step_size > 0.0)) return SWARM_ERR_CONFIG;
   if (c->dwell_normal < 0 || c->dwell_anom < 0 || c->dwell_normal > 32767 || c->dwell_anom > 32767) return SWARM_ERR_CONFIG;
   if (RC / c->step_size > 2.0e9) return SWARM_ERR_CONFIG;
@@ -190,7 +192,7 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
     const double M = std::ldexp((double)((c->row_count > c->col_count ? c->row_count : c->col_count) - 1) + c->step_size, k);
     p.f32_exact = k <= 12 && M <= 2896.0;
   }
-  p.obs_per_env = c->obs_mode == SWARM_OBS_FULL ? (int)RC : c->n_drones * c->window * c->window;
+  p.obs_per_env = c->obs_mode == SWARM_OBS_FULL ? (int)RC : (c->obs_dtype == SWARM_DTYPE_P2 ? c->n_drones : c->n_drones * c->window * c->window);
   p.ss = (float)c->step_size; p.xmax = (float)(c->row_count - 1); p.ymax = (float)(c->col_count - 1);
   p.cd = c->collision_dist;
   p.spread_thr = (double)(c->row_count / c->n_drones);
@@ -214,6 +216,10 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   }
   e->ts = pick_tile(c, sms, &p);
   e->staged = e->ts != 0;
+  if (!e->staged && c->obs_dtype == SWARM_DTYPE_P2) {   // the packed format is emitted by the staged warp kernel only
+    delete e;
+    return SWARM_ERR_CONFIG;
+  }
   if (!e->staged) e->ts = 32;
   if (e->staged) {
     // CTA shape and ring depth: the (warps per CTA w, stages S) pair with the cheapest schedule.  Model: an SM keeps `ctas`
@@ -303,7 +309,7 @@ extern "C" int swarm_create(const SwarmConfig* c, SwarmEnv** out) {
   cudaMemsetAsync(p.meta, 0, N * sizeof(int4), 0);
   p.tables = e->tables_dev;
   if (p.obs_dtype == SWARM_DTYPE_F32) build_tables_kernel<float><<<1, 256, 0, 0>>>(p, e->tables_dev);
-  else build_tables_kernel<uint8_t><<<1, 256, 0, 0>>>(p, e->tables_dev);
+  else if (p.obs_dtype == SWARM_DTYPE_U8) build_tables_kernel<uint8_t><<<1, 256, 0, 0>>>(p, e->tables_dev);   // (packed: warp kernel only, no tables)
   reset_kernel<<<grid_blocks(e, p.N), 256, 0, 0>>>(p, nullptr, 0);
   e->launches++;
   err = cudaStreamSynchronize(0);
@@ -343,7 +349,7 @@ extern "C" int swarm_get_config(const SwarmEnv* e, SwarmConfig* out) {
 
 extern "C" int64_t swarm_obs_elems(const SwarmEnv* e) { return e ? (int64_t)e->p.N * e->p.obs_per_env : 0; }
 extern "C" int64_t swarm_obs_bytes(const SwarmEnv* e) {
-  return e ? swarm_obs_elems(e) * (e->p.obs_dtype == SWARM_DTYPE_F32 ? 4 : 1) : 0;
+  return e ? swarm_obs_elems(e) * (e->p.obs_dtype == SWARM_DTYPE_F32 ? 4 : (e->p.obs_dtype == SWARM_DTYPE_P2 ? 8 : 1)) : 0;
 }
 
 extern "C" int swarm_state_ptr(SwarmEnv* e, int which, void** ptr_out, int64_t* bytes_out) {
@@ -493,8 +499,39 @@ static cudaError_t launch_step_ot(SwarmEnv* e, const StepIO& io_in, cudaStream_t
   return err;
 }
 
+// Packed 2-bit windows (SWARM_DTYPE_P2): the staged warp kernel with W == 5 only, one 64-bit word per drone.
+template <int TS>
+static cudaError_t launch_p2_ts(SwarmEnv* e, const StepIO& io, cudaStream_t st, long long blocks, int smem) {
+  const DevParams& p = e->p;
+  const bool fast = (io.flags & F_ALL) == F_ALL && p.cd_fast && !p.has_wait && p.f32_exact && (io.act_dtype == SWARM_ACT_U8 || io.T == 1);
+  const int epw = 32 / TS;
+  const bool lean = fast && io.act_dtype == SWARM_ACT_U8 && io.T == 1 && !io.obs_last_only && io.obs_out && io.stats && p.D == TS && p.N % epw == 0 && (epw * TS) % 16 == 0 &&
+                    ((((uintptr_t)io.actions) | ((uintptr_t)io.obs_out)) & 15) == 0 && !getenv("SWARM_NO_LEAN");
+  if (lean) return launch_warp_inst<TS, Packed2, 1, 5, true, true>(e, io, st, blocks, smem);
+  return fast ? launch_warp_inst<TS, Packed2, 1, 5, true>(e, io, st, blocks, smem) : launch_warp_inst<TS, Packed2, 1, 5, false>(e, io, st, blocks, smem);
+}
+
+static cudaError_t launch_step_p2(SwarmEnv* e, const StepIO& io_in, cudaStream_t st) {
+  const DevParams& p = e->p;
+  StepIO io = io_in;
+  io.dyn = e->dyn;
+  const int epw = 32 / e->ts;
+  const long long ngroups = ((long long)p.N + epw - 1) / epw;
+  const long long blocks = (ngroups + e->wpb - 1) / e->wpb;
+  cudaError_t err;
+  switch (e->ts) {
+    case 4: err = launch_p2_ts<4>(e, io, st, blocks, p.cta_smem); break;
+    case 8: err = launch_p2_ts<8>(e, io, st, blocks, p.cta_smem); break;
+    case 16: err = launch_p2_ts<16>(e, io, st, blocks, p.cta_smem); break;
+    default: err = launch_p2_ts<32>(e, io, st, blocks, p.cta_smem); break;
+  }
+  e->launches++;
+  return err;
+}
+
 static int launch_step(SwarmEnv* e, const StepIO& io, cudaStream_t st) {
-  if (e->p.obs_dtype == SWARM_DTYPE_F32) CUDA_TRY(launch_step_ot<float>(e, io, st));
+  if (e->p.obs_dtype == SWARM_DTYPE_P2) CUDA_TRY(launch_step_p2(e, io, st));
+  else if (e->p.obs_dtype == SWARM_DTYPE_F32) CUDA_TRY(launch_step_ot<float>(e, io, st));
   else CUDA_TRY(launch_step_ot<uint8_t>(e, io, st));
   CUDA_TRY(cudaGetLastError());
   return SWARM_OK;

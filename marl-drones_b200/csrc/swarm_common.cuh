@@ -179,6 +179,8 @@ constexpr uint32_t CODE_MAPPED = 0u, CODE_NORMAL = 1u, CODE_PAD = 2u, CODE_ANOM 
 // an anomaly-list entry that names no cell: (0x7000, 0x7000) is outside every LIST-mode grid (sides <= 256) and far enough
 // from the 16-bit limits for the packed window test of swarm_warp.cuh
 constexpr uint32_t LIST_EMPTY = 0x70007000u;
+// obs element type of the packed 2-bit window format (SWARM_DTYPE_P2): one word per drone, bit k = LO plane, bit 32 + k = HI plane
+using Packed2 = unsigned long long;
 
 // Is `cell` (flat index) / (x, y) one of the env's anomalous cells?
 __device__ __forceinline__ bool is_anomalous(const DevParams& p, int env, int cell, int x, int y) {

@@ -47,6 +47,11 @@ template <> struct ObsCvt<uint8_t> {
   }
 };
 
+// Packed 2-bit windows carry the codes themselves: nothing to convert (the FULL-mode emitters are never instantiated for it).
+template <> struct ObsCvt<Packed2> {
+  __device__ explicit ObsCvt(const DevParams&) {}
+};
+
 // ---- FULL obs of `nenv` consecutive envs whose coverage planes sit in shared memory (`sc`, env stride env_words words;
 // `sa`: the anomaly planes in PLANE mode, else null) by `nthr` cooperating threads (a warp or a CTA).
 // LIST mode: expand bits to 0 / 1, then — after a barrier supplied by the caller between the two calls — patch the listed

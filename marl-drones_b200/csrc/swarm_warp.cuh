@@ -65,6 +65,11 @@ __device__ __forceinline__ void emit_full_lut(const DevParams& p, const ObsCvt<O
   emit_full_patch<OT>(p, cvt, sgrid, slist, nenv, lane, 32, o);
 }
 
+// (the packed 2-bit format exists for WINDOW obs only; the FULL-mode branch of the kernel is dead code in its instantiations)
+template <>
+__device__ __forceinline__ void emit_full_lut<Packed2>(const DevParams&, const ObsCvt<Packed2>&, const uint32_t*, const uint32_t*, const uint32_t*, int, int,
+                                                       Packed2* __restrict__) {}
+
 // init_env (A2C/noVis_sim.py:36-63) for the env of this tile, built in its shared-memory stage and copied out to HBM.
 // Same RNG spec as reset_tile / oracle_reset_env.  Called by all 32 lanes; `doit` is tile-uniform; q = the lane's new position.
 template <int TS>
@@ -138,7 +143,7 @@ __global__ void __launch_bounds__(SWARM_MAXT, SWARM_MINB) step_warp_kernel(const
   const int ncg = (N + EPC - 1) / EPC;            // CTA-groups
   const bool dyn = io.dyn != 0;
   const bool want_obs = LEAN ? true : ((flags & F_OBS) && io.obs_out != nullptr);
-  const int WW = MODE == 1 ? (WC ? WC : p.W) * (WC ? WC : p.W) : 1;
+  const int WW = MODE == 1 ? (sizeof(OT) == 8 ? 1 : (WC ? WC : p.W) * (WC ? WC : p.W)) : 1;   // elements per drone (packed: one word)
   OT* const my_stage = stage + (tile * D + tl) * WW;
   // which per-group arrays may ride the bulk copy (size and address multiples of 16 B; planes, lists and meta always do)
   const bool act_tma_ok = LEAN ? true : (flags & F_MOVE) && io.act_dtype == 0 && (((uintptr_t)io.actions) & 15) == 0;

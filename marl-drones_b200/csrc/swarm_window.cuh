@@ -65,6 +65,9 @@ __device__ __forceinline__ void build_window5(int R, uint32_t sc_s, uint32_t lut
     for (int b = 0; b < 5; ++b) U |= (__funnelshift_r(w0[b], w1[b], (uint32_t)(sb + b * R)) & 31u) << (5 * b);
   }
   const uint32_t LO = U & ~P, HI = (A & U) | P;
+  if constexpr (sizeof(OT) == 8) {   // packed 2-bit format: the two planes ARE the observation
+    *st = (OT)LO | ((OT)HI << 32);
+  } else {
   uint32_t off[7];
 #pragma unroll
   for (int j = 0; j < 7; ++j) {
@@ -92,6 +95,7 @@ __device__ __forceinline__ void build_window5(int R, uint32_t sc_s, uint32_t lut
     for (int j = 0; j < 6; ++j) { o[4 * j] = (uint8_t)v[j]; o[4 * j + 1] = (uint8_t)(v[j] >> 8); o[4 * j + 2] = (uint8_t)(v[j] >> 16); o[4 * j + 3] = (uint8_t)(v[j] >> 24); }
     o[24] = (uint8_t)v[6];
   }
+  }   // not packed
 }
 
 // Generic W (any odd size): per-cell, bounds checked.  `sc`: the env's plane, `sl`: its list (shared memory).
@@ -121,10 +125,11 @@ __device__ __forceinline__ void build_window_generic(const DevParams& p, const O
 template <typename OT>
 __device__ __forceinline__ void build_window_tables(const DevParams& p, const ObsCvt<OT>& cvt, uint32_t* lut, int n_lut, uint32_t* padx, uint32_t* pady,
                                                     int tid, int nthr) {
-  for (int b = tid; b < n_lut; b += nthr) {
-    if constexpr (sizeof(OT) == 4) reinterpret_cast<float4*>(lut)[b] = cvt.quad(b & 15u, b >> 4);
-    else lut[b] = cvt.quad(b & 15u, b >> 4);
-  }
+  if constexpr (sizeof(OT) != 8)   // (the packed format needs no value table)
+    for (int b = tid; b < n_lut; b += nthr) {
+      if constexpr (sizeof(OT) == 4) reinterpret_cast<float4*>(lut)[b] = cvt.quad(b & 15u, b >> 4);
+      else lut[b] = cvt.quad(b & 15u, b >> 4);
+    }
   if (padx)
     for (int c = tid; c < 256; c += nthr) {
       uint32_t mx = 0u, my = 0u;

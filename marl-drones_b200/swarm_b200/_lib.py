@@ -19,7 +19,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 
 REWARD_A2C, REWARD_DQL = 0, 1
 OBS_FULL, OBS_WINDOW = 0, 1
-DTYPE_F32, DTYPE_U8 = 0, 1
+DTYPE_F32, DTYPE_U8, DTYPE_P2 = 0, 1, 2
 ACT_U8, ACT_I32, ACT_I64 = 0, 1, 2
 STAT_NAMES = ("env_steps", "agent_steps", "reward_sum", "episodes_done", "episode_len_sum", "episode_return_sum",
               "cells_mapped", "anomalous_mapped")

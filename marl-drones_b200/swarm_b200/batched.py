@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (ACT_I32, ACT_I64, ACT_U8, DTYPE_F32, DTYPE_U8, OBS_FULL, OBS_WINDOW, REWARD_A2C, REWARD_DQL,
+from ._lib import (ACT_I32, ACT_I64, ACT_U8, DTYPE_F32, DTYPE_P2, DTYPE_U8, OBS_FULL, OBS_WINDOW, REWARD_A2C, REWARD_DQL,
                    STAT_NAMES, SwarmConfig, SwarmError, check)
 
 _ACT_DTYPES = {torch.uint8: ACT_U8, torch.int32: ACT_I32, torch.int64: ACT_I64}
@@ -36,7 +36,9 @@ class BatchedDroneEnv:
         self._L = _lib.lib()
         rm = {"A2C": REWARD_A2C, "DQL": REWARD_DQL}[reward_mode] if isinstance(reward_mode, str) else int(reward_mode)
         om = {"full": OBS_FULL, "window": OBS_WINDOW}[obs_mode] if isinstance(obs_mode, str) else int(obs_mode)
-        od = {torch.float32: DTYPE_F32, torch.uint8: DTYPE_U8}[obs_dtype]
+        if obs_dtype == "packed2":      # SWARM_DTYPE_P2: one int64 word per drone (5x5 windows as two bit planes; unpack_windows)
+            obs_dtype = torch.int64
+        od = {torch.float32: DTYPE_F32, torch.uint8: DTYPE_U8, torch.int64: DTYPE_P2}[obs_dtype]
         self.cfg = SwarmConfig(C.sizeof(SwarmConfig), n_envs, n_drones, row_count, col_count, n_anamolous, uncertainity,
                                rm, om, window, od, int(bool(auto_reset)), dwell_normal, dwell_anom, self.device.index, 0,
                                float(collision_dist), float(step_size), seed, env_id_base)
@@ -51,6 +53,8 @@ class BatchedDroneEnv:
         self.state_size = row_count * col_count                # A2C/noVis_sim.py:30
         self.obs_dtype = obs_dtype
         self.obs_shape = (n_envs, row_count * col_count) if om == OBS_FULL else (n_envs, n_drones, window * window)
+        if od == DTYPE_P2:
+            self.obs_shape = (n_envs, n_drones)
         self.has_wait = bool(dwell_normal or dwell_anom)
         self.stats = torch.zeros(8, dtype=torch.int64, device=self.device)
         self._obs = torch.empty(self.obs_shape, dtype=obs_dtype, device=self.device)
@@ -298,3 +302,16 @@ class BatchedDroneEnv:
         """The only collective on this path: ncclAllReduce(SUM, int64[8]) of the episode statistics (64 B per rank)."""
         from .sharding import reduce_stats
         return reduce_stats(self.stats.clone(), group=group)
+
+
+def unpack_windows(packed, uncertainity=5, dtype=torch.float32):
+    """Expands packed 2-bit windows (obs_dtype="packed2", SWARM_DTYPE_P2: int64 [..., D]) into [..., D, 25] window values:
+    bit k = LO plane, bit 32 + k = HI plane of cell k = b*5 + a; code LO + 2 HI: 0 -> 0, 1 -> 1, 3 -> uncertainity, 2 -> -1
+    (255 for uint8).  Works on CPU and CUDA tensors (and numpy arrays)."""
+    if not torch.is_tensor(packed):
+        packed = torch.as_tensor(np.asarray(packed).astype(np.int64))
+    k = torch.arange(25, device=packed.device, dtype=torch.int64)
+    p = packed.to(torch.int64).unsqueeze(-1)
+    code = ((p >> k) & 1) + 2 * ((p >> (k + 32)) & 1)
+    table = torch.tensor([0, 1, 255 if dtype == torch.uint8 else -1, uncertainity], device=packed.device).to(dtype)
+    return table[code]

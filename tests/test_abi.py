@@ -92,3 +92,29 @@ def test_hot_kernel_sass_carries_what_the_design_claims():
                          ("ACQBULK", 2), ("PREEXIT", 1)):
         assert sass.count(op) >= at_least, (op, sass.count(op))
     assert "tcgen05" not in sass.lower()                         # no stage of this path is a dense contraction
+
+
+def test_packed_window_format_is_validated_without_gpu():
+    """SWARM_DTYPE_P2 (packed 2-bit windows): only WINDOW obs with W == 5; the rest is SWARM_ERR_CONFIG before any device is touched."""
+    L = _lib.lib()
+    h = C.c_void_p()
+    mk = lambda obs_mode, window: _lib.SwarmConfig(C.sizeof(_lib.SwarmConfig), 4, 3, 10, 10, 5, 5, 0, obs_mode, window, _lib.DTYPE_P2,
+                                                   1, 0, 0, 0, 0, 0.5, 1.0, 0, 0)
+    assert L.swarm_create(C.byref(mk(0, 5)), C.byref(h)) == -2          # FULL obs
+    assert L.swarm_create(C.byref(mk(1, 3)), C.byref(h)) == -2          # W != 5
+    assert L.swarm_create(C.byref(mk(1, 5)), C.byref(h)) in (0, -4)     # valid (fails on the missing device here)
+    if h.value:
+        L.swarm_destroy(h)
+    bad = mk(1, 5)
+    bad.obs_dtype = 3
+    assert L.swarm_create(C.byref(bad), C.byref(h)) == -2
+
+
+def test_unpack_windows_on_cpu():
+    import torch
+    from swarm_b200 import unpack_windows
+    lo, hi = (1 << 0) | (1 << 3) | (1 << 24), (1 << 3) | (1 << 7)
+    w = torch.tensor([[lo | (hi << 32)]], dtype=torch.int64)
+    v = unpack_windows(w, 9)
+    assert v.shape == (1, 1, 25) and v[0, 0, :8].tolist() == [1, 0, 0, 9, 0, 0, 0, -1] and v[0, 0, 24].item() == 1
+    assert unpack_windows(w, 9, torch.uint8)[0, 0, 7].item() == 255

@@ -169,6 +169,64 @@ def test_uint8_obs():
         g.close()
 
 
+@pytest.mark.parametrize("kw,N", [
+    (dict(row_count=64, col_count=64, n_drones=16, step_size=1.0), 130),                     # cfg3: LEAN instantiation
+    (dict(row_count=64, col_count=64, n_drones=16, step_size=1.0), 131),                     # ragged: FAST, partial last group
+    (dict(row_count=10, col_count=10, n_drones=3, step_size=0.5), 57),                        # fractional positions, pads everywhere
+    (dict(row_count=7, col_count=33, n_drones=8, step_size=1.0, n_anamolous=8), 64),          # rows not word-aligned
+    (dict(row_count=32, col_count=32, n_drones=32, step_size=1.0, collision_dist=1.2), 40),   # generic instantiation
+    (dict(row_count=12, col_count=12, n_drones=5, step_size=1.0, dwell=(2, 3)), 33),
+])
+def test_packed2_windows_match_oracle(kw, N):
+    """obs_dtype="packed2" (SWARM_DTYPE_P2): one 64-bit word per drone = the two bit planes of its 5x5 window.  Expanded with
+    unpack_windows it must equal the oracle's float windows (and the uint8 form) at every step; rewards / dones / state too."""
+    from swarm_b200 import unpack_windows
+    kw = dict(kw)
+    g, o = make_pair(N, auto_reset=True, seed=23, obs_mode=1, window=5, obs_dtype=torch.int64, **kw)
+    assert g.obs_shape == (N, o.D)
+    rs = np.random.RandomState(6)
+    for k in range(150):
+        a = rs.randint(0, 4, (N, o.D)).astype(np.uint8)
+        obs, rew, done, _ = g.step(torch.from_numpy(a).cuda())
+        oo, orr, od = o.step(a)
+        assert obs.dtype == torch.int64 and tuple(obs.shape) == (N, o.D)
+        vals = unpack_windows(obs, o.cfg.uncertainity if hasattr(o, "cfg") else 5).reshape(N, -1).cpu().numpy()
+        assert np.array_equal(vals, oo.astype(np.float32)), k
+        assert np.array_equal(rew.cpu().numpy(), orr.astype(np.float32)) and np.array_equal(done.cpu().numpy(), od), k
+    u8 = unpack_windows(obs, 5, torch.uint8).reshape(N, -1).cpu().numpy()
+    assert np.array_equal(u8, oo.astype(np.int16).astype(np.uint8))
+    assert_state_equal(g, o)
+    assert np.array_equal(g.stats.cpu().numpy(), o.stats)
+    # rollout and the stage entry point emit the same format
+    T = 4
+    a = rs.randint(0, 4, (T, N, o.D)).astype(np.uint8)
+    out = torch.empty((T, N, o.D), dtype=torch.int64, device="cuda")
+    g.rollout(torch.from_numpy(a).cuda(), obs_out=out)
+    for t in range(T):
+        oo, _, _ = o.step(a[t])
+        assert np.array_equal(unpack_windows(out[t], 5).reshape(N, -1).cpu().numpy(), oo.astype(np.float32)), t
+    assert np.array_equal(unpack_windows(g.stage_obs(), 5).reshape(N, -1).cpu().numpy(), oo.astype(np.float32))
+    # host-buffer step
+    obs_h = torch.empty((N, o.D), dtype=torch.int64).pin_memory()
+    a_h = torch.from_numpy(rs.randint(0, 4, (N, o.D)).astype(np.uint8)).pin_memory()
+    rew_h, done_h = torch.empty(N, dtype=torch.float32).pin_memory(), torch.empty(N, dtype=torch.uint8).pin_memory()
+    g.step_host(a_h, obs_h, rew_h, done_h)
+    oo, orr, od = o.step(a_h.numpy())
+    assert np.array_equal(unpack_windows(obs_h, 5).reshape(N, -1).numpy(), oo.astype(np.float32)) and np.array_equal(rew_h.numpy(), orr.astype(np.float32))
+    g.close()
+
+
+def test_packed2_needs_the_staged_kernel():
+    from swarm_b200 import BatchedDroneEnv, SwarmError
+    with pytest.raises(SwarmError):          # D > 32: one-CTA-per-env kernel, no packed emitter
+        BatchedDroneEnv(8, row_count=64, col_count=64, n_drones=40, step_size=1.0, obs_mode="window", window=5, obs_dtype="packed2")
+    with pytest.raises(SwarmError):          # more than 8 anomalies: PLANE mode
+        BatchedDroneEnv(8, row_count=32, col_count=32, n_drones=4, n_anamolous=12, step_size=1.0, obs_mode="window", window=5, obs_dtype="packed2")
+    g = BatchedDroneEnv(8, row_count=32, col_count=32, n_drones=4, step_size=1.0, obs_mode="window", window=5, obs_dtype="packed2")
+    assert g.obs_dtype == torch.int64 and g.obs_shape == (8, 4)
+    g.close()
+
+
 def test_action_dtypes_and_bad_action():
     g, o = make_pair(40, seed=1, **SHAPES["cfg4"])
     rs = np.random.RandomState(5)
